@@ -1,0 +1,145 @@
+/*
+ * flagg.h -- C ABI of libflagg.so, the B200 (sm_100a) robust-aggregation engine.
+ *
+ * This is the drop-in boundary for the server-side defense hot path of
+ * Shashank8834/multimodal-fl-security (reference paths below are relative to that
+ * repository).  The reference has no native code: its defenses are Python classes
+ * with the plugin interface
+ *
+ *     BaseDefense.aggregate(client_updates: List[List[Tensor]], num_examples)
+ *                                              src/defenses/base_defense.py:31-47
+ *
+ * The Python mirror of those classes (multimodal-fl-security_b200/src/defenses) binds
+ * the entry points below with ctypes; INTEGRATION.md shows the stub a maintainer of
+ * the reference would add.  No torch types cross this boundary: plain pointers,
+ * sizes and a cudaStream_t passed as void*.
+ *
+ * Conventions
+ *   - All "device" pointers are CUDA device addresses owned by the caller (the
+ *     PyTorch caching allocator in the Python mirror).  All work is enqueued on
+ *     `stream` (NULL = legacy default stream) and is asynchronous unless noted.
+ *   - Every function returns FLAGG_OK (0) or a negative flagg_status;
+ *     flagg_last_error() returns a thread-local description of the last failure.
+ *   - There is no CPU fallback anywhere in this library.
+ *
+ * The client-update "matrix" X[n, d] (n clients, d parameters) is never packed:
+ * a flagg_view describes it as n rows x P segments, segment p of client i being a
+ * contiguous fp32 device array of seg_numel[p] elements -- exactly the
+ * List[List[Tensor]] the reference passes around (krum.py:55-57 flattens it,
+ * trimmed_mean.py:79 stacks it; both copies are avoided here).
+ */
+#ifndef FLAGG_H
+#define FLAGG_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLAGG_VERSION 100 /* 0.1.0 */
+
+typedef enum flagg_status {
+    FLAGG_OK = 0,
+    FLAGG_EINVAL = -1,       /* bad argument */
+    FLAGG_ECUDA = -2,        /* CUDA runtime error (text in flagg_last_error) */
+    FLAGG_ENOMEM = -3,
+    FLAGG_EUNSUPPORTED = -4  /* valid request this build cannot serve */
+} flagg_status;
+
+typedef enum flagg_select_mode {
+    FLAGG_MEDIAN = 0,        /* rank (n-1)/2 under (value, client index) order   */
+    FLAGG_TRIMMED_MEAN = 1   /* mean of sorted ranks [k, n-k)                     */
+} flagg_select_mode;
+
+typedef struct flagg_view flagg_view;
+
+/* ---- library ---------------------------------------------------------------- */
+int flagg_version(void);
+const char* flagg_last_error(void);
+/* SM count and compute capability of the current device. */
+int flagg_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- views ------------------------------------------------------------------ */
+/* Describe n client updates of P tensors each.  seg_numel: host array [P];
+ * seg_ptrs: HOST array [n*P] of DEVICE addresses, seg_ptrs[i*P+p] = client i,
+ * tensor p (fp32, at least 4-byte aligned; 16-byte alignment enables 128-bit
+ * loads).  The small pointer tables are uploaded on `stream`; the data is not
+ * touched.  Replaces: torch.cat/torch.stack packing at krum.py:57,
+ * trimmed_mean.py:79,160, fltrust.py:91, differential_privacy.py:58,225,311. */
+int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
+                      const void* const* seg_ptrs, void* stream);
+int flagg_view_destroy(flagg_view* v);
+int64_t flagg_view_cols(const flagg_view* v); /* d = sum(seg_numel) */
+int flagg_view_rows(const flagg_view* v);     /* n */
+
+/* ---- K1: column-wise order statistics -------------------------------------- */
+/* out[d] (device, fp32, segments concatenated) = per-coordinate median or trimmed
+ * mean over the n clients.
+ *   FLAGG_MEDIAN        replaces torch.median(stacked, dim=0)[0]
+ *                       (trimmed_mean.py:101,163): bit-exact, including the
+ *                       (value, index) tie rule for +-0 and "any NaN -> first NaN".
+ *   FLAGG_TRIMMED_MEAN  replaces torch.sort + slice [k:n-k] + mean(dim=0)
+ *                       (trimmed_mean.py:82-88); requires 1 <= n-2k; NaN sorts last.
+ *                       The kept values are summed in FP64 and rounded once. */
+int flagg_colwise_select(const flagg_view* v, int mode, int k, float* out, void* stream);
+
+/* ---- K2: streaming row reductions ------------------------------------------ */
+/* One pass over X producing, per client i (device outputs, any may be NULL):
+ *   sumsq[i] = sum_c x_ic^2 (FP64)   -- torch.norm at krum.py:95 (after centring),
+ *                                       fltrust.py:175,208, differential_privacy.py:88,228,311
+ *   dot[i]   = sum_c x_ic*g0_c (FP64)-- torch.dot at fltrust.py:174 (needs g0)
+ *   linf[i]  = max_c |x_ic|          -- differential_privacy.py:230
+ *   g0_sumsq = sum_c g0_c^2          -- fltrust.py:176,209
+ * g0: device fp32 [d] (segments concatenated) or NULL.  Deterministic (fixed
+ * reduction order). */
+int flagg_row_reduce(const flagg_view* v, const float* g0, double* sumsq, double* dot,
+                     float* linf, double* g0_sumsq, void* stream);
+
+/* ---- K3: weighted row combination ------------------------------------------ */
+/* out[c] = ( ...((0 + t_0) + t_1) ... + t_{m-1}) / divisor,
+ *   t_j = w2[j] * (w1[j] * x[rows[j]][c])
+ * with every multiply, add and the final divide rounded to fp32 separately and in
+ * this order -- the arithmetic of Python's sum() over scalar*tensor products at
+ * base_defense.py:91-95, krum.py:187-190, fltrust.py:262-268,
+ * differential_privacy.py:148-155,262-269,325-332 -- so results are bit-identical to
+ * the reference's CPU path.  rows/w1/w2: HOST arrays [m] (NULL rows = 0..m-1 with
+ * m == n; NULL weight = 1.0f).  out: device fp32 [d]. */
+int flagg_row_combine(const flagg_view* v, int m, const int32_t* rows, const float* w1,
+                      const float* w2, float divisor, float* out, void* stream);
+
+/* ---- K4/K5: Krum ------------------------------------------------------------ */
+/* G (device, FP64, n*n row-major, symmetric) = (X - c)(X - c)^T where c is row
+ * `center_row` of X (0 <= center_row < n; pairwise distances are translation
+ * invariant, centring removes the common component of full-weight rows)
+ * or no centring if center_row < 0.  Replaces the O(n^2) loop of
+ * torch.norm(fi - fj) at krum.py:92-97.  With the parameter dimension sharded,
+ * partial G's add: all-reduce them before flagg_krum_scores.
+ * `accumulate` != 0 adds into G instead of overwriting it. */
+int flagg_gram(const flagg_view* v, int center_row, int accumulate, double* G, void* stream);
+
+/* D[i,j] = sqrt(max(0, G_ii + G_jj - 2 G_ij)) (un-squared, as krum.py:95), D_ii = 0;
+ * scores[i] = sum of the (n-f-2) smallest D[i,j], j != i (krum.py:122-129).
+ * D may be NULL.  All device FP64.  Requires 1 <= n-f-2 <= n-1 and n <= 4096. */
+int flagg_krum_scores(const double* G, int n, int f, double* D, double* scores, void* stream);
+
+/* ---- host-resident inputs (Flower path, robust_server.py:99-108) ------------ */
+/* Same contract as flagg_colwise_select, but seg_ptrs are HOST addresses (pinned
+ * memory gives full PCIe rate) and out is a HOST buffer [d].  Columns are streamed
+ * through the GPU in chunks of `chunk_cols` (0 = default) with copies and kernels
+ * overlapped on internal streams; returns after the result is in `out`. */
+int flagg_colwise_select_host(int n, int P, const int64_t* seg_numel,
+                              const void* const* host_seg_ptrs, int mode, int k,
+                              float* host_out, int64_t chunk_cols);
+
+/* Copy n host rows (P segments each) into one dense device matrix dst[n, ld]
+ * (ld >= d, fp32), chunked and asynchronous on `stream`.  Used to make host inputs
+ * resident for the two-pass defenses (Krum, FLTrust, clipping). */
+int flagg_upload_rows(int n, int P, const int64_t* seg_numel,
+                      const void* const* host_seg_ptrs, float* dst, int64_t ld, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLAGG_H */

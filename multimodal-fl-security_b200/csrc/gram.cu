@@ -1,0 +1,218 @@
+// K4: centred Gram matrix G = (X - c)(X - c)^T in FP64 (upper triangle computed, mirrored)
+// K5: Krum distances and scores from G.
+//
+// Replaces the n(n-1)/2 Python iterations of torch.norm(flat_i - flat_j).item() at
+// krum.py:92-97 (O(n^2 d) bytes of traffic, one host sync per pair) and the per-client
+// np.sort / np.sum at krum.py:122-129.
+//
+// Precision: rows are full weight vectors, so ||x||^2 >> ||x_i - x_j||^2.
+// Every element is centred on a common row before it is multiplied (distances are
+// translation invariant), products are accumulated in fp32 for at most 1024 columns and
+// then folded into FP64; D^2 and sqrt are formed in FP64.
+//
+// This file is the CUDA-core (FFMA) implementation: 64x64 output tiles, split-K across
+// the grid with a deterministic two-stage reduction.  gram_tc.cu (3xTF32 on tcgen05) is
+// the tensor-core path for large n.
+#include "common.cuh"
+
+namespace flagg {
+
+constexpr int GT = 64;          // output tile edge
+constexpr int GK = 32;          // columns per k-step (128 B of every row)
+constexpr int G_THREADS = 256;  // 16 x 16 threads, 4 x 4 outputs each
+constexpr int G_FLUSH_UNITS = 8;  // fold fp32 -> fp64 every 8 x 128 columns
+
+// Stage GK columns of rows [r0, r0+64) into sm[k][row] (centred, zero padded).
+__device__ __forceinline__ void gram_stage(const ViewDev& v, int p, int64_t col0, int valid, int r0,
+                                           const float* __restrict__ crow, float (*sm)[GT + 1]) {
+    const int tid = threadIdx.x, kcol = tid & 31, rsub = tid >> 5;
+    const bool ok = kcol < valid;
+    const float cval = (ok && crow) ? __ldg(crow + col0 + kcol) : 0.f;
+#pragma unroll
+    for (int j = 0; j < GT / 8; ++j) {
+        const int r = r0 + rsub + 8 * j;
+        float x = 0.f;
+        if (ok && r < v.n) x = ldg_stream(v.seg_ptrs[size_t(r) * v.P + p] + col0 + kcol) - cval;
+        sm[kcol][rsub + 8 * j] = x;
+    }
+}
+
+// grid = (tiles, splits).  Tile t -> (bi <= bj).  Split s owns 128-column units
+// [s*upb, (s+1)*upb).  Writes its 64x64 FP64 partial to part[(s*tiles + t)*4096 ...].
+__global__ void __launch_bounds__(G_THREADS)
+gram_ffma_kernel(ViewDev v, int center_row, int nb, int64_t total_units, int64_t units_per_split,
+                 double* __restrict__ part) {
+    __shared__ float As[GK][GT + 1];
+    __shared__ float Bs[GK][GT + 1];
+    // decode upper-triangular tile index
+    int t = blockIdx.x, bi = 0;
+    while (t >= nb - bi) { t -= nb - bi; ++bi; }
+    const int bj = bi + t;
+    const bool diag = (bi == bj);
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const int64_t* __restrict__ ustart = v.unit_start[GRAN_128];
+
+    double acc64[4][4];
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { acc64[i][j] = 0.0; acc[i][j] = 0.f; }
+
+    const int64_t u0 = int64_t(blockIdx.y) * units_per_split;
+    const int64_t u1 = min(total_units, u0 + units_per_split);
+    int since_flush = 0;
+    for (int64_t u = u0; u < u1; ++u) {
+        const int p = find_segment(ustart, v.P, u);
+        const int64_t c0 = (u - ustart[p]) * 128;
+        const int len = int(min((long long)(128), (long long)v.seg_start[p + 1] - v.seg_start[p] - c0));
+        const float* crow = center_row >= 0 ? v.seg_ptrs[size_t(center_row) * v.P + p] : nullptr;
+        for (int ks = 0; ks < len; ks += GK) {
+            __syncthreads();
+            gram_stage(v, p, c0 + ks, len - ks, bi * GT, crow, As);
+            if (!diag) gram_stage(v, p, c0 + ks, len - ks, bj * GT, crow, Bs);
+            __syncthreads();
+            float (*Bp)[GT + 1] = diag ? As : Bs;
+#pragma unroll
+            for (int kk = 0; kk < GK; ++kk) {
+                float a[4], b[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { a[i] = As[kk][ty * 4 + i]; b[i] = Bp[kk][tx * 4 + i]; }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+            }
+        }
+        if (++since_flush == G_FLUSH_UNITS) {
+            since_flush = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { acc64[i][j] += double(acc[i][j]); acc[i][j] = 0.f; }
+        }
+    }
+    double* dst = part + (size_t(blockIdx.y) * gridDim.x + blockIdx.x) * (GT * GT);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            dst[(ty * 4 + i) * GT + tx * 4 + j] = acc64[i][j] + double(acc[i][j]);
+}
+
+// Sum the split partials in split order and scatter the tile (and its mirror) into G.
+__global__ void gram_reduce_kernel(const double* __restrict__ part, int tiles, int splits, int nb, int n,
+                                   int accumulate, double* __restrict__ G) {
+    int t = blockIdx.x, bi = 0;
+    while (t >= nb - bi) { t -= nb - bi; ++bi; }
+    const int bj = bi + t;
+    for (int e = threadIdx.x; e < GT * GT; e += blockDim.x) {
+        const int r = bi * GT + e / GT, c = bj * GT + e % GT;
+        if (r >= n || c >= n) continue;
+        if (bi == bj && c < r) continue;  // diagonal tile: lower half comes from the mirror
+        double s = 0.0;
+        for (int sp = 0; sp < splits; ++sp) s += part[(size_t(sp) * tiles + blockIdx.x) * (GT * GT) + e];
+        if (accumulate) {
+            G[size_t(r) * n + c] += s;
+            if (r != c) G[size_t(c) * n + r] += s;
+        } else {
+            G[size_t(r) * n + c] = s;
+            if (r != c) G[size_t(c) * n + r] = s;
+        }
+    }
+}
+
+// ---- K5 ------------------------------------------------------------------------------
+// One CTA per client i: D_ij in shared memory, bitonic sort, sum of ranks 1..m
+// (rank 0 is the self distance 0, as np.sort(row)[1:m+1] at krum.py:126-129).
+__global__ void __launch_bounds__(256)
+krum_scores_kernel(const double* __restrict__ G, int n, int npad, int m, double* __restrict__ D,
+                   double* __restrict__ scores) {
+    extern __shared__ double srow[];  // [npad]
+    __shared__ double red[256];
+    const int i = blockIdx.x, tid = threadIdx.x;
+    const double gii = G[size_t(i) * n + i];
+    for (int j = tid; j < npad; j += blockDim.x) {
+        double dv = __longlong_as_double(0x7ff0000000000000LL);  // +inf padding
+        if (j < n) {
+            const double d2 = gii + G[size_t(j) * n + j] - 2.0 * G[size_t(i) * n + j];
+            dv = (j == i) ? 0.0 : sqrt(fmax(d2, 0.0));
+            if (D) D[size_t(i) * n + j] = dv;
+        }
+        srow[j] = dv;
+    }
+    __syncthreads();
+    for (int k = 2; k <= npad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int x = tid; x < npad; x += blockDim.x) {
+                const int y = x ^ j;
+                if (y > x) {
+                    const double a = srow[x], b = srow[y];
+                    const bool up = ((x & k) == 0);
+                    if ((a > b) == up) { srow[x] = b; srow[y] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    double s = 0.0;
+    for (int j = 1 + tid; j <= m; j += blockDim.x) s += srow[j];
+    red[tid] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (tid < o) red[tid] += red[tid + o];
+        __syncthreads();
+    }
+    if (tid == 0) scores[i] = red[0];
+}
+
+}  // namespace flagg
+
+using namespace flagg;
+
+extern "C" {
+
+int flagg_gram(const flagg_view* cv, int center_row, int accumulate, double* G, void* stream) {
+    FLAGG_REQUIRE(cv && G, "flagg_gram: NULL argument");
+    flagg_view* v = const_cast<flagg_view*>(cv);
+    const int n = v->dev.n;
+    FLAGG_REQUIRE(center_row < n, "flagg_gram: center_row %d out of range (n=%d)", center_row, n);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nb = (n + GT - 1) / GT;
+    const int tiles = nb * (nb + 1) / 2;
+    const int64_t units = v->total_units[GRAN_128];
+    if (units == 0) {
+        if (!accumulate) FLAGG_CUDA(cudaMemsetAsync(G, 0, sizeof(double) * size_t(n) * n, st));
+        return FLAGG_OK;
+    }
+    const int sms = device_sm_count();
+    int64_t splits = std::max<int64_t>(1, (int64_t(sms) * 4 + tiles - 1) / tiles);
+    splits = std::min<int64_t>(splits, units);
+    splits = std::min<int64_t>(splits, 65535);
+    const int64_t upb = (units + splits - 1) / splits;
+    splits = (units + upb - 1) / upb;
+    const size_t need = sizeof(double) * size_t(splits) * tiles * GT * GT;
+    int rc = v->ensure_scratch(need);
+    if (rc != FLAGG_OK) return rc;
+    double* part = static_cast<double*>(v->d_scratch);
+    dim3 grid(tiles, unsigned(splits));
+    gram_ffma_kernel<<<grid, G_THREADS, 0, st>>>(v->dev, center_row, nb, units, upb, part);
+    FLAGG_CUDA(cudaGetLastError());
+    gram_reduce_kernel<<<tiles, 256, 0, st>>>(part, tiles, int(splits), nb, n, accumulate, G);
+    FLAGG_CUDA(cudaGetLastError());
+    return FLAGG_OK;
+}
+
+int flagg_krum_scores(const double* G, int n, int f, double* D, double* scores, void* stream) {
+    FLAGG_REQUIRE(G && scores, "flagg_krum_scores: NULL argument");
+    const int m = n - f - 2;
+    FLAGG_REQUIRE(n >= 1 && n <= 4096, "flagg_krum_scores: n=%d unsupported (1..4096)", n);
+    FLAGG_REQUIRE(m >= 1 && m <= n - 1, "flagg_krum_scores: need 1 <= n-f-2 <= n-1 (n=%d f=%d)", n, f);
+    int npad = 2;
+    while (npad < n) npad <<= 1;
+    krum_scores_kernel<<<n, 256, sizeof(double) * npad, static_cast<cudaStream_t>(stream)>>>(G, n, npad, m, D, scores);
+    FLAGG_CUDA(cudaGetLastError());
+    return FLAGG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,135 @@
+// Host-resident inputs: the Flower server path hands the defense CPU tensors
+// (robust_server.py:99-108) and wants CPU tensors back (:125).  Columns are streamed
+// through the GPU in chunks, H2D copies of chunk c+1 overlapping the select kernel and
+// the D2H copy of chunk c (two internal streams, three staging buffers).  PCIe-bound by
+// construction; reported separately from the HBM roofline (bench.py "e2e").
+#include <algorithm>
+
+#include "common.cuh"
+
+using namespace flagg;
+
+namespace {
+
+struct HostPipe {
+    static constexpr int NBUF = 3;
+    float* stage[NBUF] = {nullptr, nullptr, nullptr};
+    float* outb[NBUF] = {nullptr, nullptr, nullptr};
+    flagg_view* view[NBUF] = {nullptr, nullptr, nullptr};
+    cudaEvent_t filled[NBUF] = {}, drained[NBUF] = {};
+    cudaStream_t s_copy = nullptr, s_comp = nullptr;
+    bool ev_ok = false;
+    ~HostPipe() {
+        for (int b = 0; b < NBUF; ++b) {
+            if (view[b]) flagg_view_destroy(view[b]);
+            if (stage[b]) cudaFree(stage[b]);
+            if (outb[b]) cudaFree(outb[b]);
+            if (ev_ok) { cudaEventDestroy(filled[b]); cudaEventDestroy(drained[b]); }
+        }
+        if (s_copy) cudaStreamDestroy(s_copy);
+        if (s_comp) cudaStreamDestroy(s_comp);
+    }
+};
+
+int make_dense_view(flagg_view** out, float* base, int n, int64_t ld, int64_t cols, cudaStream_t st) {
+    std::vector<const void*> ptrs(n);
+    for (int i = 0; i < n; ++i) ptrs[i] = base + size_t(i) * ld;
+    return flagg_view_create(out, n, 1, &cols, ptrs.data(), st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int flagg_colwise_select_host(int n, int P, const int64_t* seg_numel, const void* const* host_seg_ptrs,
+                              int mode, int k, float* host_out, int64_t chunk_cols) {
+    FLAGG_REQUIRE(seg_numel && host_seg_ptrs && host_out, "flagg_colwise_select_host: NULL argument");
+    FLAGG_REQUIRE(n >= 1 && P >= 1, "flagg_colwise_select_host: need n >= 1 and P >= 1");
+    if (mode == FLAGG_TRIMMED_MEAN)
+        FLAGG_REQUIRE(k >= 0 && n - 2 * k >= 1, "flagg_colwise_select_host: trimmed mean needs n-2k >= 1 (n=%d k=%d)", n, k);
+    std::vector<int64_t> seg_start(P + 1, 0);
+    for (int p = 0; p < P; ++p) {
+        FLAGG_REQUIRE(seg_numel[p] >= 0, "flagg_colwise_select_host: negative segment size");
+        seg_start[p + 1] = seg_start[p] + seg_numel[p];
+    }
+    const int64_t d = seg_start[P];
+    if (d == 0) return FLAGG_OK;
+    if (chunk_cols <= 0) chunk_cols = std::max<int64_t>(128 * 1024, (int64_t(256) << 20) / (4 * int64_t(n)));
+    chunk_cols = std::min<int64_t>((chunk_cols + 127) & ~int64_t(127), (d + 127) & ~int64_t(127));
+    const int64_t nchunks = (d + chunk_cols - 1) / chunk_cols;
+
+    HostPipe hp;
+    FLAGG_CUDA(cudaStreamCreateWithFlags(&hp.s_copy, cudaStreamNonBlocking));
+    FLAGG_CUDA(cudaStreamCreateWithFlags(&hp.s_comp, cudaStreamNonBlocking));
+    const int nbuf = int(std::min<int64_t>(HostPipe::NBUF, nchunks));
+    for (int b = 0; b < HostPipe::NBUF; ++b) {
+        FLAGG_CUDA(cudaEventCreateWithFlags(&hp.filled[b], cudaEventDisableTiming));
+        FLAGG_CUDA(cudaEventCreateWithFlags(&hp.drained[b], cudaEventDisableTiming));
+    }
+    hp.ev_ok = true;
+    for (int b = 0; b < nbuf; ++b) {
+        FLAGG_CUDA(cudaMalloc(&hp.stage[b], sizeof(float) * size_t(n) * chunk_cols));
+        FLAGG_CUDA(cudaMalloc(&hp.outb[b], sizeof(float) * size_t(chunk_cols)));
+        int rc = make_dense_view(&hp.view[b], hp.stage[b], n, chunk_cols, chunk_cols, hp.s_comp);
+        if (rc != FLAGG_OK) return rc;
+    }
+    flagg_view* tail_view = nullptr;  // the last chunk is usually narrower
+    int rc = FLAGG_OK;
+    for (int64_t ch = 0; ch < nchunks && rc == FLAGG_OK; ++ch) {
+        const int b = int(ch % nbuf);
+        const int64_t c0 = ch * chunk_cols, c1 = std::min(d, c0 + chunk_cols), w = c1 - c0;
+        if (ch >= nbuf) FLAGG_CUDA(cudaStreamWaitEvent(hp.s_copy, hp.drained[b], 0));
+        // first segment overlapping [c0, c1)
+        int p0 = int(std::upper_bound(seg_start.begin(), seg_start.end(), c0) - seg_start.begin()) - 1;
+        for (int i = 0; i < n; ++i) {
+            for (int p = p0; p < P && seg_start[p] < c1; ++p) {
+                const int64_t a = std::max(c0, seg_start[p]), e = std::min(c1, seg_start[p + 1]);
+                if (e <= a) continue;
+                const float* src = static_cast<const float*>(host_seg_ptrs[size_t(i) * P + p]) + (a - seg_start[p]);
+                FLAGG_CUDA(cudaMemcpyAsync(hp.stage[b] + size_t(i) * chunk_cols + (a - c0), src,
+                                           sizeof(float) * size_t(e - a), cudaMemcpyHostToDevice, hp.s_copy));
+            }
+        }
+        FLAGG_CUDA(cudaEventRecord(hp.filled[b], hp.s_copy));
+        FLAGG_CUDA(cudaStreamWaitEvent(hp.s_comp, hp.filled[b], 0));
+        const flagg_view* use = hp.view[b];
+        if (w != chunk_cols) {
+            rc = make_dense_view(&tail_view, hp.stage[b], n, chunk_cols, w, hp.s_comp);
+            if (rc != FLAGG_OK) break;
+            use = tail_view;
+        }
+        rc = flagg_colwise_select(use, mode, k, hp.outb[b], hp.s_comp);
+        if (rc != FLAGG_OK) break;
+        FLAGG_CUDA(cudaMemcpyAsync(host_out + c0, hp.outb[b], sizeof(float) * size_t(w), cudaMemcpyDeviceToHost, hp.s_comp));
+        FLAGG_CUDA(cudaEventRecord(hp.drained[b], hp.s_comp));
+    }
+    cudaError_t e1 = cudaStreamSynchronize(hp.s_copy), e2 = cudaStreamSynchronize(hp.s_comp);
+    if (tail_view) flagg_view_destroy(tail_view);
+    if (rc != FLAGG_OK) return rc;
+    if (e1 != cudaSuccess || e2 != cudaSuccess) {
+        set_error("flagg_colwise_select_host: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+        return FLAGG_ECUDA;
+    }
+    return FLAGG_OK;
+}
+
+int flagg_upload_rows(int n, int P, const int64_t* seg_numel, const void* const* host_seg_ptrs, float* dst,
+                      int64_t ld, void* stream) {
+    FLAGG_REQUIRE(seg_numel && host_seg_ptrs && dst, "flagg_upload_rows: NULL argument");
+    int64_t d = 0;
+    for (int p = 0; p < P; ++p) d += seg_numel[p];
+    FLAGG_REQUIRE(ld >= d, "flagg_upload_rows: ld (%lld) < d (%lld)", (long long)ld, (long long)d);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    for (int i = 0; i < n; ++i) {
+        int64_t off = 0;
+        for (int p = 0; p < P; ++p) {
+            if (seg_numel[p] > 0)
+                FLAGG_CUDA(cudaMemcpyAsync(dst + size_t(i) * ld + off, host_seg_ptrs[size_t(i) * P + p],
+                                           sizeof(float) * size_t(seg_numel[p]), cudaMemcpyHostToDevice, st));
+            off += seg_numel[p];
+        }
+    }
+    return FLAGG_OK;
+}
+
+}  // extern "C"

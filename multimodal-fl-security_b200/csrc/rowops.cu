@@ -1,0 +1,306 @@
+// K2: streaming row reductions (||x_i||^2, x_i . g0, max|x_i|, ||g0||^2) in ONE pass
+//     over the client-update matrix -- replaces the per-client torch.cat + torch.norm
+//     + torch.dot calls at fltrust.py:170-176,205-209 and
+//     differential_privacy.py:87-88,225-230,311.
+// K3: weighted row combination with the reference's exact fp32 operation order --
+//     replaces Python sum() over scalar*tensor at base_defense.py:91-95,
+//     krum.py:187-190, fltrust.py:262-268, differential_privacy.py:148-155,262-269,325-332.
+// Both are HBM-bound streaming kernels: 128-bit coalesced loads, no shared-memory
+// staging of X (no reuse), grid sized from the SM count.
+#include "common.cuh"
+
+namespace flagg {
+
+constexpr int RR_THREADS = 256;
+constexpr int RR_WARPS = RR_THREADS / 32;
+constexpr int RR_CHUNK = 2048;  // == unit_cols(GRAN_2K): 8 KB of each row per unit
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Persistent CTAs; CTA b walks units b, b+grid, ...  Within a unit warp w owns rows
+// w, w+8, ...: each lane streams 16 x float4 of the row (8 KB per warp-row, all loads
+// independent), multiplies in fp32, accumulates float4-partials in FP64, and the warp
+// total lands in the CTA's shared per-row accumulator (one owner warp per row: no
+// atomics).  Per-CTA partials go to `part`; row_reduce_finalize adds them in CTA order,
+// so the result is deterministic.
+template <bool VEC4, bool HAS_G0>
+__global__ void __launch_bounds__(RR_THREADS)
+row_reduce_kernel(ViewDev v, const float* __restrict__ g0, double* __restrict__ part_ss,
+                  double* __restrict__ part_dot, float* __restrict__ part_linf,
+                  double* __restrict__ part_g0, int64_t total_units) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int n = v.n;
+    double* acc_ss = reinterpret_cast<double*>(smem_raw);
+    double* acc_dot = acc_ss + n;
+    float* g0s = reinterpret_cast<float*>(acc_dot + n);   // [RR_CHUNK], 16 B aligned (n*16 bytes before)
+    float* acc_inf = g0s + RR_CHUNK;
+    __shared__ double red[RR_WARPS];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < n; i += RR_THREADS) { acc_ss[i] = 0.0; acc_dot[i] = 0.0; acc_inf[i] = 0.f; }
+    double g0ss = 0.0;
+    const int64_t* __restrict__ ustart = v.unit_start[GRAN_2K];
+
+    for (int64_t u = blockIdx.x; u < total_units; u += gridDim.x) {
+        const int p = find_segment(ustart, v.P, u);
+        const int64_t c0 = (u - ustart[p]) * RR_CHUNK;
+        const int64_t segn = v.seg_start[p + 1] - v.seg_start[p];
+        const int len = int(min((long long)(RR_CHUNK), (long long)segn - c0));
+        __syncthreads();  // previous unit's readers of g0s are done (also orders the init above)
+        if (HAS_G0) {
+            const float* gsrc = g0 + v.seg_start[p] + c0;
+            for (int j = tid; j < RR_CHUNK; j += RR_THREADS) {
+                float g = (j < len) ? __ldg(gsrc + j) : 0.f;
+                g0s[j] = g;
+                g0ss += double(g * g);
+            }
+            __syncthreads();
+        }
+        const int nv = VEC4 ? (len >> 2) : 0;
+        for (int i = warp; i < n; i += RR_WARPS) {
+            const float* row = v.seg_ptrs[size_t(i) * v.P + p] + c0;
+            double ss = 0.0, dt = 0.0;
+            float mx = 0.f;
+            if (VEC4) {
+                const float4* row4 = reinterpret_cast<const float4*>(row);
+                const float4* g4 = reinterpret_cast<const float4*>(g0s);
+                float4 x[16];
+#pragma unroll
+                for (int jj = 0; jj < 16; ++jj) {
+                    const int j = lane + 32 * jj;
+                    x[jj] = (j < nv) ? ldg_stream4(row4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int jj = 0; jj < 16; ++jj) {
+                    const int j = lane + 32 * jj;
+                    const float4 a = x[jj];
+                    ss += double((a.x * a.x + a.y * a.y) + (a.z * a.z + a.w * a.w));
+                    mx = fmaxf(fmaxf(mx, fmaxf(fabsf(a.x), fabsf(a.y))), fmaxf(fabsf(a.z), fabsf(a.w)));
+                    if (HAS_G0) {
+                        const float4 g = g4[j & (RR_CHUNK / 4 - 1)];
+                        dt += double((a.x * g.x + a.y * g.y) + (a.z * g.z + a.w * g.w));
+                    }
+                }
+            }
+            for (int j = (nv << 2) + lane; j < len; j += 32) {   // tail / unaligned path
+                const float a = ldg_stream(row + j);
+                ss += double(a * a);
+                mx = fmaxf(mx, fabsf(a));
+                if (HAS_G0) dt += double(a * g0s[j]);
+            }
+            ss = warp_sum(ss);
+            mx = warp_max(mx);
+            if (HAS_G0) dt = warp_sum(dt);
+            if (lane == 0) {
+                acc_ss[i] += ss;
+                acc_inf[i] = fmaxf(acc_inf[i], mx);
+                if (HAS_G0) acc_dot[i] += dt;
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += RR_THREADS) {
+        part_ss[size_t(blockIdx.x) * n + i] = acc_ss[i];
+        part_dot[size_t(blockIdx.x) * n + i] = acc_dot[i];
+        part_linf[size_t(blockIdx.x) * n + i] = acc_inf[i];
+    }
+    g0ss = warp_sum(g0ss);
+    if (lane == 0) red[warp] = g0ss;
+    __syncthreads();
+    if (tid == 0) {
+        double t = 0.0;
+        for (int w = 0; w < RR_WARPS; ++w) t += red[w];
+        part_g0[blockIdx.x] = t;
+    }
+}
+
+__global__ void row_reduce_finalize(const double* __restrict__ part_ss, const double* __restrict__ part_dot,
+                                    const float* __restrict__ part_linf, const double* __restrict__ part_g0,
+                                    int nblocks, int n, double* sumsq, double* dot, float* linf, double* g0_sumsq) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        double ss = 0.0, dt = 0.0;
+        float mx = 0.f;
+        for (int b = 0; b < nblocks; ++b) {
+            ss += part_ss[size_t(b) * n + i];
+            dt += part_dot[size_t(b) * n + i];
+            mx = fmaxf(mx, part_linf[size_t(b) * n + i]);
+        }
+        if (sumsq) sumsq[i] = ss;
+        if (dot) dot[i] = dt;
+        // torch.max(torch.abs(x)) propagates NaN (differential_privacy.py:230); fmaxf does not.
+        if (linf) linf[i] = (ss != ss) ? __int_as_float(0x7fc00000) : mx;
+    }
+    if (i == 0 && g0_sumsq) {
+        double t = 0.0;
+        for (int b = 0; b < nblocks; ++b) t += part_g0[b];
+        *g0_sumsq = t;
+    }
+}
+
+// ---- K3 ----------------------------------------------------------------------------
+constexpr int RC_THREADS = 256;
+constexpr int RC_UNROLL = 8;
+
+// One CTA per 1024-column unit; thread owns 4 columns.  The m selected rows are visited
+// strictly in order; loads of RC_UNROLL rows are issued together, then folded in with
+// separately rounded multiply / multiply / add (no FMA contraction) so the result is
+// bit-identical to the reference's left-to-right Python sum().
+template <bool VEC4>
+__global__ void __launch_bounds__(RC_THREADS)
+row_combine_kernel(ViewDev v, int m, const int* __restrict__ rows, const float* __restrict__ w1,
+                   const float* __restrict__ w2, float divisor, float* __restrict__ out) {
+    const int64_t* __restrict__ ustart = v.unit_start[GRAN_1K];
+    const int64_t u = blockIdx.x;
+    const int p = find_segment(ustart, v.P, u);
+    const int64_t c0 = (u - ustart[p]) * 1024;
+    const int64_t segn = v.seg_start[p + 1] - v.seg_start[p];
+    const int len = int(min((long long)(1024), (long long)segn - c0));
+    const int t = threadIdx.x;
+    int col[4];
+    bool vec = false;
+    if (VEC4 && 4 * t + 3 < len) {
+        vec = true;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) col[q] = 4 * t + q;
+    } else if (VEC4) {
+        // ragged tail of a vectorised unit: the few leftover columns go to the threads
+        // past the last full float4, one column each
+        const int full = len >> 2;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) col[q] = (q == 0 && t >= full && 4 * full + (t - full) < len) ? 4 * full + (t - full) : -1;
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) col[q] = (t + RC_THREADS * q < len) ? t + RC_THREADS * q : -1;
+    }
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int j0 = 0; j0 < m; j0 += RC_UNROLL) {
+        float x[RC_UNROLL][4];
+        float a1[RC_UNROLL], a2[RC_UNROLL];
+#pragma unroll
+        for (int jj = 0; jj < RC_UNROLL; ++jj) {
+            const int j = j0 + jj;
+            if (j < m) {
+                const float* row = v.seg_ptrs[size_t(__ldg(rows + j)) * v.P + p] + c0;
+                a1[jj] = __ldg(w1 + j);
+                a2[jj] = __ldg(w2 + j);
+                if (vec) {
+                    const float4 q4 = ldg_stream4(reinterpret_cast<const float4*>(row) + t);
+                    x[jj][0] = q4.x; x[jj][1] = q4.y; x[jj][2] = q4.z; x[jj][3] = q4.w;
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) x[jj][q] = (col[q] >= 0) ? ldg_stream(row + col[q]) : 0.f;
+                }
+            }
+        }
+#pragma unroll
+        for (int jj = 0; jj < RC_UNROLL; ++jj) {
+            if (j0 + jj < m) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    acc[q] = __fadd_rn(acc[q], __fmul_rn(a2[jj], __fmul_rn(a1[jj], x[jj][q])));
+            }
+        }
+    }
+    float* o = out + v.seg_start[p] + c0;
+    if (vec && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+        float4 r;
+        r.x = __fdiv_rn(acc[0], divisor); r.y = __fdiv_rn(acc[1], divisor);
+        r.z = __fdiv_rn(acc[2], divisor); r.w = __fdiv_rn(acc[3], divisor);
+        reinterpret_cast<float4*>(o)[t] = r;
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            if (col[q] >= 0) o[col[q]] = __fdiv_rn(acc[q], divisor);
+    }
+}
+
+}  // namespace flagg
+
+using namespace flagg;
+
+extern "C" {
+
+int flagg_row_reduce(const flagg_view* cv, const float* g0, double* sumsq, double* dot, float* linf,
+                     double* g0_sumsq, void* stream) {
+    FLAGG_REQUIRE(cv, "flagg_row_reduce: NULL view");
+    FLAGG_REQUIRE(!(dot && !g0), "flagg_row_reduce: dot requested without g0");
+    FLAGG_REQUIRE(!(g0_sumsq && !g0), "flagg_row_reduce: g0_sumsq requested without g0");
+    flagg_view* v = const_cast<flagg_view*>(cv);
+    const int n = v->dev.n;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t units = v->total_units[GRAN_2K];
+    const size_t smem = size_t(n) * 16 + RR_CHUNK * 4 + size_t(n) * 4;
+    FLAGG_REQUIRE(smem <= 200 * 1024, "flagg_row_reduce: n=%d too large for the per-CTA accumulators", n);
+    int nblocks = int(std::min<int64_t>(std::max<int64_t>(units, 1), int64_t(device_sm_count()) * 4));
+    const size_t b_d = sizeof(double) * size_t(nblocks) * n;
+    const size_t b_f = sizeof(float) * size_t(nblocks) * n;
+    const size_t need = 2 * b_d + ((b_f + 7) & ~size_t(7)) + sizeof(double) * nblocks;
+    int rc = v->ensure_scratch(need);
+    if (rc != FLAGG_OK) return rc;
+    char* s = static_cast<char*>(v->d_scratch);
+    double* part_ss = reinterpret_cast<double*>(s);
+    double* part_dot = reinterpret_cast<double*>(s + b_d);
+    double* part_g0 = reinterpret_cast<double*>(s + 2 * b_d);
+    float* part_linf = reinterpret_cast<float*>(s + 2 * b_d + sizeof(double) * nblocks);
+    const bool vec4 = v->align_bytes >= 16;
+    auto launch = [&](auto kern) -> int {
+        FLAGG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        kern<<<nblocks, RR_THREADS, smem, st>>>(v->dev, g0, part_ss, part_dot, part_linf, part_g0, units);
+        FLAGG_CUDA(cudaGetLastError());
+        return FLAGG_OK;
+    };
+    if (vec4 && g0) rc = launch(row_reduce_kernel<true, true>);
+    else if (vec4) rc = launch(row_reduce_kernel<true, false>);
+    else if (g0) rc = launch(row_reduce_kernel<false, true>);
+    else rc = launch(row_reduce_kernel<false, false>);
+    if (rc != FLAGG_OK) return rc;
+    row_reduce_finalize<<<(n + 127) / 128, 128, 0, st>>>(part_ss, part_dot, part_linf, part_g0, nblocks, n,
+                                                         sumsq, dot, linf, g0_sumsq);
+    FLAGG_CUDA(cudaGetLastError());
+    return FLAGG_OK;
+}
+
+int flagg_row_combine(const flagg_view* cv, int m, const int32_t* rows, const float* w1, const float* w2,
+                      float divisor, float* out, void* stream) {
+    FLAGG_REQUIRE(cv && out, "flagg_row_combine: NULL argument");
+    flagg_view* v = const_cast<flagg_view*>(cv);
+    const int n = v->dev.n;
+    FLAGG_REQUIRE(m >= 1, "flagg_row_combine: m must be >= 1 (got %d)", m);
+    FLAGG_REQUIRE(rows || m == n, "flagg_row_combine: rows == NULL requires m == n");
+    std::vector<int32_t> hr(m);
+    std::vector<float> hw(2 * size_t(m));
+    for (int j = 0; j < m; ++j) {
+        hr[j] = rows ? rows[j] : j;
+        FLAGG_REQUIRE(hr[j] >= 0 && hr[j] < n, "flagg_row_combine: rows[%d]=%d out of range", j, hr[j]);
+        hw[j] = w1 ? w1[j] : 1.0f;
+        hw[m + j] = w2 ? w2[j] : 1.0f;
+    }
+    int rc = v->ensure_scratch(sizeof(float) * 3 * size_t(m) + 64);
+    if (rc != FLAGG_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    float* d_w = static_cast<float*>(v->d_scratch);
+    int* d_rows = reinterpret_cast<int*>(d_w + 2 * size_t(m));
+    FLAGG_CUDA(cudaMemcpyAsync(d_w, hw.data(), sizeof(float) * 2 * size_t(m), cudaMemcpyHostToDevice, st));
+    FLAGG_CUDA(cudaMemcpyAsync(d_rows, hr.data(), sizeof(int32_t) * size_t(m), cudaMemcpyHostToDevice, st));
+    const int64_t units = v->total_units[GRAN_1K];
+    if (units == 0) return FLAGG_OK;
+    FLAGG_REQUIRE(units < (int64_t(1) << 31), "flagg_row_combine: too many column units");
+    if (v->align_bytes >= 16)
+        row_combine_kernel<true><<<unsigned(units), RC_THREADS, 0, st>>>(v->dev, m, d_rows, d_w, d_w + m, divisor, out);
+    else
+        row_combine_kernel<false><<<unsigned(units), RC_THREADS, 0, st>>>(v->dev, m, d_rows, d_w, d_w + m, divisor, out);
+    FLAGG_CUDA(cudaGetLastError());
+    return FLAGG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,136 @@
+// flagg_view: the n x P segmented description of the client-update matrix, plus
+// library-level plumbing (error string, device info).
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace flagg {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int device_sm_count() {
+    static thread_local int cached_dev = -1, cached = 0;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev != cached_dev) {
+        cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
+        cached_dev = dev;
+    }
+    return cached > 0 ? cached : 148;
+}
+
+}  // namespace flagg
+
+using namespace flagg;
+
+int flagg_view::ensure_scratch(size_t bytes) {
+    if (bytes <= scratch_bytes) return FLAGG_OK;
+    if (d_scratch) FLAGG_CUDA(cudaFree(d_scratch));
+    d_scratch = nullptr;
+    scratch_bytes = 0;
+    size_t want = (bytes + 0xffff) & ~size_t(0xffff);
+    FLAGG_CUDA(cudaMalloc(&d_scratch, want));
+    scratch_bytes = want;
+    return FLAGG_OK;
+}
+
+extern "C" {
+
+int flagg_version(void) { return FLAGG_VERSION; }
+
+const char* flagg_last_error(void) { return g_err; }
+
+int flagg_device_info(int* sm_count, int* cc_major, int* cc_minor) {
+    int dev = 0;
+    FLAGG_CUDA(cudaGetDevice(&dev));
+    int v = 0;
+    if (sm_count) { FLAGG_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev)); *sm_count = v; }
+    if (cc_major) { FLAGG_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMajor, dev)); *cc_major = v; }
+    if (cc_minor) { FLAGG_CUDA(cudaDeviceGetAttribute(&v, cudaDevAttrComputeCapabilityMinor, dev)); *cc_minor = v; }
+    return FLAGG_OK;
+}
+
+int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
+                      const void* const* seg_ptrs, void* stream) {
+    FLAGG_REQUIRE(out && seg_numel && seg_ptrs, "flagg_view_create: NULL argument");
+    FLAGG_REQUIRE(n >= 1 && P >= 1, "flagg_view_create: need n >= 1 and P >= 1 (got n=%d P=%d)", n, P);
+    flagg_view* v = new (std::nothrow) flagg_view();
+    if (!v) { set_error("flagg_view_create: out of host memory"); return FLAGG_ENOMEM; }
+    v->seg_numel.assign(seg_numel, seg_numel + P);
+    v->seg_start.resize(P + 1);
+    v->seg_start[0] = 0;
+    for (int g = 0; g < NUM_GRAN; ++g) v->unit_start[g].assign(P + 1, 0);
+    for (int p = 0; p < P; ++p) {
+        if (seg_numel[p] < 0) { delete v; set_error("flagg_view_create: negative segment size"); return FLAGG_EINVAL; }
+        v->seg_start[p + 1] = v->seg_start[p] + seg_numel[p];
+        for (int g = 0; g < NUM_GRAN; ++g)
+            v->unit_start[g][p + 1] = v->unit_start[g][p] + (seg_numel[p] + unit_cols(g) - 1) / unit_cols(g);
+    }
+    for (int g = 0; g < NUM_GRAN; ++g) v->total_units[g] = v->unit_start[g][P];
+    v->seg_ptrs.assign(seg_ptrs, seg_ptrs + size_t(n) * P);
+    int align = 16;
+    for (size_t i = 0; i < v->seg_ptrs.size(); ++i) {
+        uintptr_t a = reinterpret_cast<uintptr_t>(v->seg_ptrs[i]);
+        if (a == 0 && v->seg_numel[i % P] > 0) { delete v; set_error("flagg_view_create: NULL segment pointer"); return FLAGG_EINVAL; }
+        if (a & 3) { delete v; set_error("flagg_view_create: segment pointer not 4-byte aligned"); return FLAGG_EINVAL; }
+        if (v->seg_numel[i % P] == 0) continue;
+        if (a & 15) align = (a & 7) ? 4 : (align < 8 ? align : 8);
+    }
+    v->align_bytes = align;
+    cudaError_t e = cudaGetDevice(&v->device);
+    if (e != cudaSuccess) { delete v; set_error("cudaGetDevice: %s", cudaGetErrorString(e)); return FLAGG_ECUDA; }
+
+    const size_t b_ptrs = sizeof(void*) * size_t(n) * P;
+    const size_t b_pref = sizeof(int64_t) * (P + 1);
+    const size_t total = b_ptrs + (1 + NUM_GRAN) * b_pref;
+    e = cudaMalloc(&v->d_tables, total);
+    if (e != cudaSuccess) { delete v; set_error("cudaMalloc(view tables, %zu B): %s", total, cudaGetErrorString(e)); return FLAGG_ECUDA; }
+    char* base = static_cast<char*>(v->d_tables);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // Pageable sources: cudaMemcpyAsync stages them before returning, so the host
+    // vectors may change afterwards; ordering w.r.t. later kernels is by stream.
+    e = cudaMemcpyAsync(base, v->seg_ptrs.data(), b_ptrs, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(base + b_ptrs, v->seg_start.data(), b_pref, cudaMemcpyHostToDevice, st);
+    for (int g = 0; g < NUM_GRAN && e == cudaSuccess; ++g)
+        e = cudaMemcpyAsync(base + b_ptrs + (1 + g) * b_pref, v->unit_start[g].data(), b_pref, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) {
+        set_error("flagg_view_create: table upload failed: %s", cudaGetErrorString(e));
+        cudaFree(v->d_tables);
+        delete v;
+        return FLAGG_ECUDA;
+    }
+    v->dev.seg_ptrs = reinterpret_cast<const float* const*>(base);
+    v->dev.seg_start = reinterpret_cast<const int64_t*>(base + b_ptrs);
+    for (int g = 0; g < NUM_GRAN; ++g)
+        v->dev.unit_start[g] = reinterpret_cast<const int64_t*>(base + b_ptrs + (1 + g) * b_pref);
+    v->dev.n = n;
+    v->dev.P = P;
+    v->dev.d = v->seg_start[P];
+    *out = v;
+    return FLAGG_OK;
+}
+
+int flagg_view_destroy(flagg_view* v) {
+    if (!v) return FLAGG_OK;
+    cudaError_t e1 = v->d_tables ? cudaFree(v->d_tables) : cudaSuccess;
+    cudaError_t e2 = v->d_scratch ? cudaFree(v->d_scratch) : cudaSuccess;
+    delete v;
+    if (e1 != cudaSuccess || e2 != cudaSuccess) {
+        set_error("flagg_view_destroy: cudaFree failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+        return FLAGG_ECUDA;
+    }
+    return FLAGG_OK;
+}
+
+int64_t flagg_view_cols(const flagg_view* v) { return v ? v->dev.d : -1; }
+int flagg_view_rows(const flagg_view* v) { return v ? v->dev.n : -1; }
+
+}  // extern "C"

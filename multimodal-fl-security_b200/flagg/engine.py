@@ -1,0 +1,232 @@
+"""Host side of the engine: turns the reference's ``List[List[Tensor]]`` into a
+flagg_view (pointer table, no packing copy) and launches the kernels of libflagg.so on
+the caller's current CUDA stream.  torch is used for device memory and streams only.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import FlaggError, MEDIAN, TRIMMED_MEAN, check, lib
+
+
+def _require_cuda() -> None:
+    if not torch.cuda.is_available():
+        raise FlaggError("flagg needs a CUDA device (sm_100a); there is no CPU fallback")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+class Updates:
+    """n client updates of P tensors each, as the defenses receive them
+    (base_defense.py:31-35).  Device tensors are used in place; host tensors stay on the
+    host until a kernel needs them (``resident()`` uploads them once)."""
+
+    def __init__(self, client_updates: Sequence[Sequence[torch.Tensor]]):
+        if len(client_updates) == 0:
+            raise ValueError("client_updates is empty")
+        self.n = len(client_updates)
+        self.P = len(client_updates[0])
+        if self.P == 0:
+            raise ValueError("client updates hold no tensors")
+        first = client_updates[0]
+        self.shapes = [tuple(t.shape) for t in first]
+        self.numel = [int(t.numel()) for t in first]
+        self.in_dtypes = [t.dtype for t in first]
+        self.d = int(sum(self.numel))
+        self.on_host = not first[0].is_cuda
+        self.device = first[0].device
+        rows = []
+        for i, upd in enumerate(client_updates):
+            if len(upd) != self.P:
+                raise ValueError(f"client {i} has {len(upd)} tensors, expected {self.P}")
+            row = []
+            for p, t in enumerate(upd):
+                if int(t.numel()) != self.numel[p]:
+                    raise ValueError(f"client {i} tensor {p}: {tuple(t.shape)} != {self.shapes[p]}")
+                if t.is_cuda == self.on_host:
+                    raise ValueError("client updates mix host and device tensors")
+                # every reference defense .float()s on flatten/stack (krum.py:57, trimmed_mean.py:79)
+                t = t.detach()
+                if t.dtype != torch.float32 or not t.is_contiguous():
+                    t = t.to(torch.float32).contiguous()
+                row.append(t)
+            rows.append(row)
+        self.rows = rows          # keeps every tensor alive while a view points at it
+        self._view = None
+        self._dense = None
+
+    # -- views ---------------------------------------------------------------------
+    def _ptr_tables(self):
+        seg = (C.c_int64 * self.P)(*self.numel)
+        ptrs = (C.c_void_p * (self.n * self.P))()
+        k = 0
+        for row in self.rows:
+            for t in row:
+                ptrs[k] = t.data_ptr()
+                k += 1
+        return seg, ptrs
+
+    def resident(self) -> "Updates":
+        """Device-resident version of these updates (uploads host rows into one dense
+        [n, ld] matrix with flagg_upload_rows; a no-op for device inputs)."""
+        if not self.on_host:
+            return self
+        if self._dense is None:
+            _require_cuda()
+            ld = (self.d + 3) & ~3
+            X = torch.empty((self.n, ld), dtype=torch.float32, device="cuda")
+            seg, ptrs = self._ptr_tables()
+            check(lib().flagg_upload_rows(self.n, self.P, seg, ptrs, X.data_ptr(), ld, _stream()), "flagg_upload_rows")
+            offs = np.concatenate([[0], np.cumsum(self.numel)])
+            lists = [[X[i, offs[p]:offs[p + 1]] for p in range(self.P)] for i in range(self.n)]
+            dev = Updates(lists)
+            dev.shapes, dev.in_dtypes = self.shapes, self.in_dtypes
+            dev._keep = X
+            self._dense = dev
+        return self._dense
+
+    def view(self) -> int:
+        if self.on_host:
+            raise FlaggError("internal: view() on host-resident updates")
+        if self._view is None:
+            _require_cuda()
+            seg, ptrs = self._ptr_tables()
+            h = C.c_void_p()
+            with torch.cuda.device(self.device):
+                check(lib().flagg_view_create(C.byref(h), self.n, self.P, seg, ptrs, _stream()), "flagg_view_create")
+            self._view = h
+        return self._view
+
+    def close(self) -> None:
+        if self._view is not None:
+            lib().flagg_view_destroy(self._view)
+            self._view = None
+        if self._dense is not None:
+            self._dense.close()
+            self._dense = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- result shaping --------------------------------------------------------------
+    def split(self, flat: torch.Tensor, to_host: bool, dtypes=None) -> List[torch.Tensor]:
+        """Flat [d] result -> list of P tensors shaped like the inputs, on the inputs' device."""
+        if to_host and flat.is_cuda:
+            flat = flat.cpu()
+        out, off = [], 0
+        for p in range(self.P):
+            t = flat[off:off + self.numel[p]].reshape(self.shapes[p])
+            if dtypes is not None and dtypes[p] != t.dtype:
+                t = t.to(dtypes[p])
+            out.append(t)
+            off += self.numel[p]
+        return out
+
+
+# ---------------------------------------------------------------------------------------
+# kernels
+# ---------------------------------------------------------------------------------------
+def colwise_select(u: Updates, mode: int, k: int = 0) -> torch.Tensor:
+    """K1.  Returns the flat fp32 result [d] on the inputs' device (host inputs are
+    streamed through the GPU by flagg_colwise_select_host and come back on the host)."""
+    _require_cuda()
+    if u.on_host:
+        out = torch.empty(u.d, dtype=torch.float32)
+        seg, ptrs = u._ptr_tables()
+        check(lib().flagg_colwise_select_host(u.n, u.P, seg, ptrs, mode, k, out.data_ptr(), 0),
+              "flagg_colwise_select_host")
+        return out
+    with torch.cuda.device(u.device):
+        out = torch.empty(u.d, dtype=torch.float32, device=u.device)
+        check(lib().flagg_colwise_select(u.view(), mode, k, out.data_ptr(), _stream()), "flagg_colwise_select")
+    return out
+
+
+def row_stats(u: Updates, g0_flat: Optional[torch.Tensor] = None, group=None) -> dict:
+    """K2.  One pass over X: per-client sum of squares, dot with g0 (FP64) and max |x|.
+    With ``group`` (a torch.distributed process group; X sharded by parameters) the
+    partial sums are all-reduced so every rank gets whole-vector statistics."""
+    u = u.resident()
+    with torch.cuda.device(u.device):
+        n = u.n
+        buf = torch.zeros(2 * n + 1, dtype=torch.float64, device=u.device)
+        linf = torch.zeros(n, dtype=torch.float32, device=u.device)
+        g_ptr = None
+        if g0_flat is not None:
+            g0_flat = g0_flat.to(device=u.device, dtype=torch.float32).contiguous()
+            if g0_flat.numel() != u.d:
+                raise ValueError("g0 has the wrong number of elements")
+            g_ptr = g0_flat.data_ptr()
+        p = buf.data_ptr()
+        check(lib().flagg_row_reduce(u.view(), g_ptr, p, (p + 8 * n) if g_ptr else None, linf.data_ptr(),
+                                     (p + 16 * n) if g_ptr else None, _stream()), "flagg_row_reduce")
+        if group is not None:
+            import torch.distributed as dist
+            dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+            dist.all_reduce(linf, op=dist.ReduceOp.MAX, group=group)
+        h = buf.cpu().numpy()
+        return dict(sumsq=h[:n].copy(), dot=h[n:2 * n].copy(), g0_sumsq=float(h[2 * n]),
+                    linf=linf.cpu().numpy())
+
+
+def row_combine(u: Updates, rows, w1, w2, divisor: float) -> torch.Tensor:
+    """K3.  Flat fp32 [d] = (sum_j w2_j*(w1_j*x_rows[j])) / divisor, reference order."""
+    u = u.resident()
+    m = len(rows) if rows is not None else u.n
+    def arr(x, ct):
+        if x is None:
+            return None
+        a = np.ascontiguousarray(x, dtype=np.float32 if ct is C.c_float else np.int32)
+        if a.size != m:
+            raise ValueError("weight / row arrays must have one entry per combined row")
+        return a.ctypes.data_as(C.POINTER(ct)), a
+    r = arr(rows, C.c_int32)
+    a1 = arr(w1, C.c_float)
+    a2 = arr(w2, C.c_float)
+    with torch.cuda.device(u.device):
+        out = torch.empty(u.d, dtype=torch.float32, device=u.device)
+        check(lib().flagg_row_combine(u.view(), m, r[0] if r else None, a1[0] if a1 else None,
+                                      a2[0] if a2 else None, float(np.float32(divisor)), out.data_ptr(), _stream()),
+              "flagg_row_combine")
+    return out
+
+
+def gram(u: Updates, center_row: int = 0, group=None) -> torch.Tensor:
+    """K4.  FP64 centred Gram matrix [n, n] on the device; all-reduced over ``group``
+    when the parameter dimension is sharded (partial Grams add)."""
+    u = u.resident()
+    with torch.cuda.device(u.device):
+        G = torch.empty((u.n, u.n), dtype=torch.float64, device=u.device)
+        check(lib().flagg_gram(u.view(), center_row, 0, G.data_ptr(), _stream()), "flagg_gram")
+        if group is not None:
+            import torch.distributed as dist
+            dist.all_reduce(G, op=dist.ReduceOp.SUM, group=group)
+    return G
+
+
+def krum_scores(G: torch.Tensor, f: int, want_D: bool = True):
+    """K5.  (D [n,n] float64 ndarray or None, scores [n] float64 ndarray)."""
+    n = G.shape[0]
+    with torch.cuda.device(G.device):
+        scores = torch.empty(n, dtype=torch.float64, device=G.device)
+        D = torch.empty((n, n), dtype=torch.float64, device=G.device) if want_D else None
+        check(lib().flagg_krum_scores(G.data_ptr(), n, f, D.data_ptr() if want_D else None, scores.data_ptr(),
+                                      _stream()), "flagg_krum_scores")
+        return (D.cpu().numpy() if want_D else None), scores.cpu().numpy()
+
+
+def device_info() -> dict:
+    _require_cuda()
+    a, b, c = C.c_int(), C.c_int(), C.c_int()
+    check(lib().flagg_device_info(C.byref(a), C.byref(b), C.byref(c)), "flagg_device_info")
+    return dict(sm_count=a.value, cc=(b.value, c.value))

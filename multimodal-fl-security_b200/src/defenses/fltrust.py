@@ -1,0 +1,128 @@
+"""FLTrust -- mirrors /root/reference/src/defenses/fltrust.py:17-308.
+
+Trust scores and the renormalisation both need whole-row reductions, so the update
+matrix is read twice: K2 produces every ||x_i||^2, x_i.g0 and ||g0||^2 in one pass
+(replacing n flatten+dot+2 norms, fltrust.py:170-176, and n more flatten+norms,
+:205-209), K3 applies ts_i * (x_i * ||g0||/||x_i||) / sum(ts) in the reference's
+operation order (:262-268).  The server-gradient step (:93-150) is model training, not
+aggregation, and stays in PyTorch.
+"""
+from typing import Any, Dict, List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.optim as optim
+from torch.utils.data import DataLoader, Dataset, Subset
+
+from flagg import engine
+from .base_defense import BaseDefense
+
+
+class FLTrustDefense(BaseDefense):
+    def __init__(self, defense_config: Dict[str, Any]):
+        super().__init__(defense_config)
+        self.root_dataset_size = defense_config.get('root_dataset_size', 100)
+        self.learning_rate = defense_config.get('learning_rate', 0.01)
+        self.local_epochs = defense_config.get('local_epochs', 1)
+        self.batch_size = defense_config.get('batch_size', 32)
+        self.root_dataset = None
+        self.model = None
+        self.device = defense_config.get('device', 'cpu')
+        self.trust_scores = []
+        self.server_gradient = None
+
+    def set_root_dataset(self, dataset: Dataset) -> None:
+        if len(dataset) > self.root_dataset_size:            # fltrust.py:75-83
+            idx = np.random.choice(len(dataset), size=self.root_dataset_size, replace=False)
+            self.root_dataset = Subset(dataset, idx.tolist())
+        else:
+            self.root_dataset = dataset
+
+    def set_model(self, model: nn.Module) -> None:
+        self.model = model.to(self.device)
+
+    def _flatten(self, tensors: List[torch.Tensor]) -> torch.Tensor:
+        return torch.cat([t.flatten().float() for t in tensors])
+
+    def _compute_server_gradient(self, global_params: List[torch.Tensor]) -> List[torch.Tensor]:
+        """One short SGD run on the root dataset; g0 = theta_after - theta_before
+        (fltrust.py:93-150).  Plain PyTorch: this is training, not the aggregation path."""
+        if self.root_dataset is None:
+            raise ValueError("Root dataset not set. Call set_root_dataset() first.")
+        if self.model is None:
+            raise ValueError("Model not set. Call set_model() first.")
+        sd = self.model.state_dict()
+        for i, key in enumerate(sd.keys()):
+            sd[key] = global_params[i].clone()
+        self.model.load_state_dict(sd)
+        before = [p.clone() for p in global_params]
+        self.model.train()
+        loss_fn = nn.CrossEntropyLoss()
+        opt = optim.SGD(self.model.parameters(), lr=self.learning_rate, momentum=0.9)
+        loader = DataLoader(self.root_dataset, batch_size=self.batch_size, shuffle=True)
+        for _ in range(self.local_epochs):
+            for images, labels in loader:
+                images, labels = images.to(self.device), labels.to(self.device)
+                opt.zero_grad()
+                loss_fn(self.model(images), labels).backward()
+                opt.step()
+        after = [p.data.clone() for p in self.model.parameters()]
+        self.server_gradient = [after[i] - before[i] for i in range(len(before))]
+        return self.server_gradient
+
+    # kept for API parity; the engine computes all of these at once in aggregate()
+    def _compute_trust_score(self, client_update, server_gradient) -> float:
+        u = engine.Updates([client_update])
+        st = engine.row_stats(u, self._flatten(server_gradient), group=self._group)
+        return self._trust_from_stats(st)[0][0]
+
+    @staticmethod
+    def _trust_from_stats(st):
+        """fp32 arithmetic of fltrust.py:174-186 and :208-214 on the K2 reductions."""
+        f32 = np.float32
+        sn = f32(np.sqrt(st['g0_sumsq']))
+        trust, scale = [], []
+        with np.errstate(all='ignore'):
+            for ss, dot in zip(st['sumsq'], st['dot']):
+                cn = f32(np.sqrt(ss))
+                if cn < 1e-10 or sn < 1e-10:
+                    trust.append(0.0)
+                else:
+                    trust.append(max(0.0, float(f32(dot) / f32(cn * sn))))
+                scale.append(f32(1.0) if cn < 1e-10 else f32(sn / cn))
+        return trust, scale
+
+    def aggregate(self, client_updates, num_examples, global_params: Optional[List[torch.Tensor]] = None):
+        if global_params is None:
+            raise ValueError("global_params must be provided for FLTrust")     # fltrust.py:235-238
+        server_gradient = self._compute_server_gradient(global_params)
+        u = engine.Updates(client_updates)
+        st = engine.row_stats(u, self._flatten(server_gradient), group=self._group)
+        self.trust_scores, scale = self._trust_from_stats(st)
+        total_trust = sum(self.trust_scores)
+        if total_trust < 1e-10:                                                 # :258-260
+            return server_gradient
+        # Zero-trust rows contribute exactly +-0 to the running sum (which starts at +0 and
+        # can never be -0), so they are skipped unless the row holds Inf/NaN (0*Inf = NaN).
+        rows = [i for i in range(u.n) if self.trust_scores[i] != 0.0 or not np.isfinite(st['sumsq'][i])]
+        flat = engine.row_combine(u, rows, [scale[i] for i in rows],
+                                  [np.float32(self.trust_scores[i]) for i in rows], np.float32(total_trust))
+        dt = [d if d.is_floating_point else torch.float32 for d in u.in_dtypes]
+        return u.split(flat, to_host=u.on_host, dtypes=dt)
+
+    def detect_malicious(self, client_updates, num_examples, threshold: float = 0.1) -> List[int]:
+        if not self.trust_scores:
+            return []
+        return [i for i, s in enumerate(self.trust_scores) if s < threshold]
+
+    def get_metrics(self) -> Dict[str, Any]:
+        return {
+            'defense_type': 'fltrust',
+            'root_dataset_size': self.root_dataset_size,
+            'trust_scores': self.trust_scores,
+            'avg_trust': np.mean(self.trust_scores) if self.trust_scores else 0.0,
+        }
+
+    def __repr__(self) -> str:
+        return f"FLTrustDefense(root_size={self.root_dataset_size})"

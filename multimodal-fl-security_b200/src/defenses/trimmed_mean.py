@@ -1,0 +1,98 @@
+"""Trimmed mean / median / geometric median -- mirrors
+/root/reference/src/defenses/trimmed_mean.py:14-272.
+
+Median and trimmed mean are one launch of K1 (column-wise order statistics) over the
+un-packed update lists; the geometric median's Weiszfeld loop is composed from K1
+(initial point), K2-style distances and K3 (weighted combine).
+"""
+from typing import Any, Dict, List
+
+import numpy as np
+import torch
+
+from flagg import engine, MEDIAN, TRIMMED_MEAN
+from .base_defense import BaseDefense
+
+
+def _f32_lists(u: engine.Updates, flat: torch.Tensor):
+    return u.split(flat, to_host=u.on_host)        # .float() outputs, trimmed_mean.py:79,160
+
+
+class TrimmedMeanDefense(BaseDefense):
+    def __init__(self, defense_config: Dict[str, Any]):
+        super().__init__(defense_config)
+        self.trim_ratio = defense_config.get('trim_ratio', 0.1)
+        self.num_trimmed_per_end = 0
+
+    def aggregate(self, client_updates, num_examples):
+        n = len(client_updates)
+        self.num_trimmed_per_end = max(1, int(n * self.trim_ratio))     # trimmed_mean.py:66
+        if n - 2 * self.num_trimmed_per_end < 1:                        # :69-72
+            return self._coordinate_wise_median(client_updates)
+        u = engine.Updates(client_updates)
+        return _f32_lists(u, engine.colwise_select(u, TRIMMED_MEAN, self.num_trimmed_per_end))
+
+    def _coordinate_wise_median(self, client_updates):
+        u = engine.Updates(client_updates)
+        return _f32_lists(u, engine.colwise_select(u, MEDIAN))
+
+    def get_metrics(self) -> Dict[str, Any]:
+        return {'defense_type': 'trimmed_mean', 'trim_ratio': self.trim_ratio,
+                'num_trimmed_per_end': self.num_trimmed_per_end}
+
+    def __repr__(self) -> str:
+        return f"TrimmedMeanDefense(trim_ratio={self.trim_ratio})"
+
+
+class MedianDefense(BaseDefense):
+    def __init__(self, defense_config: Dict[str, Any] = None):
+        super().__init__(defense_config or {})
+
+    def aggregate(self, client_updates, num_examples):
+        u = engine.Updates(client_updates)
+        return _f32_lists(u, engine.colwise_select(u, MEDIAN))
+
+    def get_metrics(self) -> Dict[str, Any]:
+        return {'defense_type': 'median'}
+
+    def __repr__(self) -> str:
+        return "MedianDefense()"
+
+
+class GeometricMedianDefense(BaseDefense):
+    """Weiszfeld iterations (trimmed_mean.py:225-265): start at the coordinate-wise
+    median, then x <- sum_i(u_i / ||u_i - x||) / sum_i(1 / ||u_i - x||)."""
+
+    def __init__(self, defense_config: Dict[str, Any] = None):
+        super().__init__(defense_config or {})
+        self.max_iters = defense_config.get('max_iters', 100) if defense_config else 100
+        self.tolerance = defense_config.get('tolerance', 1e-5) if defense_config else 1e-5
+        self.num_iters = 0
+
+    def aggregate(self, client_updates, num_examples):
+        u = engine.Updates(client_updates).resident()
+        n = u.n
+        current = engine.colwise_select(u, MEDIAN)                       # :240
+        for iteration in range(self.max_iters):
+            # ||u_i - x||^2 = ||u_i||^2 - 2 u_i.x + ||x||^2 would cancel badly; use the
+            # centred Gram row instead: append x as an extra "client" and centre on it.
+            ext = engine.Updates([row for row in u.rows] + [[current]] if u.P == 1 else
+                                 [row for row in u.rows] + [u.split(current, to_host=False)])
+            G = engine.gram(ext, center_row=n, group=self._group)
+            dist = torch.sqrt(torch.clamp(torch.diagonal(G)[:n], min=0.0)).to(torch.float32)
+            dist = torch.clamp(dist, min=1e-10)                          # :248
+            w = (1.0 / dist)                                             # :251
+            wsum = w.sum()
+            new = engine.row_combine(u, list(range(n)), w.cpu().numpy(), None, float(wsum))
+            change = torch.norm(new - current)
+            current = new
+            ext.close()
+            if change < self.tolerance:                                  # :258-260
+                self.num_iters = iteration + 1
+                break
+        else:
+            self.num_iters = self.max_iters
+        return u.split(current, to_host=client_updates[0][0].is_cuda is False)
+
+    def get_metrics(self) -> Dict[str, Any]:
+        return {'defense_type': 'geometric_median', 'max_iters': self.max_iters, 'num_iters': self.num_iters}

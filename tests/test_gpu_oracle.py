@@ -1,0 +1,244 @@
+"""GPU parity, part 2: the C-ABI (through flagg.engine) against the oracle on seeded
+inputs at sizes the oracle finishes in seconds -- every network size, the radix
+fallback, ragged / unaligned segments, edge values -- plus size-independent properties at
+BASELINE.json's full sizes."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import assert_close_scaled, bits
+from oracle import oracle64, ref_port
+
+pytestmark = pytest.mark.gpu
+
+EDGE = np.array([0.0, -0.0, 1.0, -1.0, 2.5, np.inf, -np.inf, 1e-38, -1e-38, 1e30], dtype=np.float32)
+
+
+def rows_model(rng, n, d, byz=0):
+    theta = rng.normal(0, 0.05, d)
+    X = theta[None, :] + rng.normal(0, 1e-3, (n, d))
+    for b in range(byz):
+        X[b] = theta + 10 * (X[b] - theta)
+    return X.astype(np.float32)
+
+
+def dev_lists(X, seg=None):
+    """Rows as separately allocated device tensors (list-of-lists, like run_experiments.py:238)."""
+    n, d = X.shape
+    seg = seg or [d]
+    offs = np.concatenate([[0], np.cumsum(seg)]).astype(int)
+    return [[torch.from_numpy(X[i, offs[p]:offs[p + 1]].copy()).cuda() for p in range(len(seg))] for i in range(n)]
+
+
+def run_select(X, mode, k=0, seg=None):
+    from flagg import engine
+    u = engine.Updates(dev_lists(X, seg))
+    out = engine.colwise_select(u, mode, k).cpu().numpy()
+    u.close()
+    return out
+
+
+@pytest.mark.parametrize("n", list(range(1, 41)) + [44, 47, 48, 50, 63, 64, 65, 71, 72, 96, 99, 100, 101, 127, 128])
+def test_median_every_network_size(n):
+    from flagg import MEDIAN
+    rng = np.random.RandomState(1000 + n)
+    d = 777
+    X = rows_model(rng, n, d, byz=n // 5)
+    X[:, :200] = rng.choice(EDGE, size=(n, 200))
+    X[:, 200:232] = rng.choice(np.array([0.0, -0.0], dtype=np.float32), size=(n, 32))   # mixed-sign zero columns
+    Xi = X.view(np.uint32)
+    for j in range(232, 260):
+        Xi[rng.randint(n), j] = rng.choice([0x7FC00000, 0xFFC00001, 0x7F800123])        # NaN payloads
+    got = run_select(X, MEDIAN, seg=[300, 77, 400])
+    assert np.array_equal(bits(got), bits(oracle64.median_stable(X))), n
+
+
+@pytest.mark.parametrize("n", [129, 130, 200, 257, 1000])
+def test_median_radix_fallback(n):
+    from flagg import MEDIAN
+    rng = np.random.RandomState(n)
+    d = 300
+    X = rows_model(rng, n, d, byz=n // 10)
+    X[:, :100] = rng.choice(EDGE, size=(n, 100))
+    X.view(np.uint32)[rng.randint(n), 101] = 0x7FC00001
+    got = run_select(X, MEDIAN, seg=[260, 40])
+    assert np.array_equal(bits(got), bits(oracle64.median_stable(X)))
+
+
+@pytest.mark.parametrize("n,k", [(3, 1), (5, 1), (5, 2), (10, 1), (20, 2), (20, 4), (33, 9), (64, 6), (100, 10),
+                                 (100, 28), (128, 12), (129, 12), (300, 30), (1000, 100)])
+def test_trimmed_mean_vs_oracle(n, k):
+    from flagg import TRIMMED_MEAN
+    rng = np.random.RandomState(7 * n + k)
+    d = 1100 if n <= 128 else 260
+    X = rows_model(rng, n, d, byz=min(k, n // 5))
+    X[:k // 2 + 1] *= 100.0                                          # scaling attackers
+    X[:, :64] = rng.choice(np.array([0.0, -0.0, 1.0, -1.0, 2.5, 1e-38, 1e30], dtype=np.float32), size=(n, 64))
+    X.view(np.uint32)[rng.randint(n), 70] = 0x7FC00000               # one NaN: sorts last and is trimmed
+    got = run_select(X, TRIMMED_MEAN, k, seg=[d - 100, 100])
+    ref, kk, fb = ref_port.trimmed_mean(torch.from_numpy(X), k / n + 1e-9)
+    assert kk == k and not fb
+    assert_close_scaled(got, ref.numpy(), oracle64.trimmed_scale(X, k), what=f"n={n} k={k}")
+    # and against the FP64 statement, tighter: one rounding of the exact mean
+    t64 = oracle64.trimmed_mean64(X, k)
+    assert_close_scaled(got, t64, oracle64.trimmed_scale(X, k), tol=2e-7, what="fp64")
+
+
+def test_trimmed_mean_nan_kept_and_inf():
+    from flagg import TRIMMED_MEAN
+    n, k, d = 9, 1, 130
+    X = np.random.RandomState(3).normal(size=(n, d)).astype(np.float32)
+    X[2, 0] = np.nan; X[5, 0] = np.nan           # two NaNs, k=1: one survives the trim -> NaN
+    X[1, 1] = np.inf; X[7, 1] = np.inf           # +inf kept -> +inf
+    X[1, 2] = np.inf; X[3, 2] = -np.inf; X[4, 2] = np.inf; X[6, 2] = -np.inf   # +inf and -inf kept -> NaN
+    got = run_select(X, TRIMMED_MEAN, k)
+    ref = ref_port.trimmed_mean(torch.from_numpy(X), k / n + 1e-9)[0].numpy()
+    assert np.array_equal(np.isnan(got), np.isnan(ref))
+    assert np.isnan(got[0]) and np.isposinf(got[1]) and np.isnan(got[2])
+    fin = np.isfinite(ref)
+    np.testing.assert_allclose(got[fin], ref[fin], rtol=1e-5, atol=1e-6)
+
+
+def test_select_unaligned_and_ragged_segments():
+    """Rows that are 4-byte-aligned views (odd offsets into one buffer) and tiny / empty segments."""
+    from flagg import MEDIAN, engine
+    rng = np.random.RandomState(11)
+    n, seg = 7, [1, 0, 3, 129, 127, 2, 1025]
+    d = sum(seg)
+    X = rng.normal(size=(n, d)).astype(np.float32)
+    big = torch.zeros(n * (d + 3) + 8, device="cuda")
+    offs = np.concatenate([[0], np.cumsum(seg)]).astype(int)
+    lists = []
+    for i in range(n):
+        base = i * (d + 3) + 1                                       # +1 float: only 4-byte aligned
+        big[base:base + d] = torch.from_numpy(X[i]).cuda()
+        lists.append([big[base + offs[p]:base + offs[p + 1]] for p in range(len(seg))])
+    u = engine.Updates(lists)
+    got = engine.colwise_select(u, MEDIAN).cpu().numpy()
+    assert np.array_equal(bits(got), bits(oracle64.median_stable(X)))
+    st = engine.row_stats(u, torch.from_numpy(X[0]).cuda())
+    np.testing.assert_allclose(st["sumsq"], oracle64.row_sumsq64(X), rtol=1e-6)
+    np.testing.assert_allclose(st["dot"], oracle64.row_dot64(X, X[0]), rtol=1e-5, atol=1e-4)
+    w = rng.uniform(0.5, 2, n).astype(np.float32)
+    comb = engine.row_combine(u, None, w, None, 3.0).cpu().numpy()
+    assert np.array_equal(bits(comb), bits(oracle64.combine_seq32(X, w, None, 3.0)))
+    u.close()
+
+
+@pytest.mark.parametrize("n,d,seg", [(10, 421642, [288, 32, 18432, 64, 401408, 128, 1280, 10]),   # C1: SimpleCNN
+                                     (37, 50000, [50000]), (500, 20011, [20000, 11])])
+def test_row_stats_and_combine_vs_oracle(n, d, seg):
+    from flagg import engine
+    rng = np.random.RandomState(n)
+    X = rows_model(rng, n, d, byz=2)
+    g = rng.normal(0, 1e-3, d).astype(np.float32)
+    u = engine.Updates(dev_lists(X, seg))
+    st = engine.row_stats(u, torch.from_numpy(g).cuda())
+    np.testing.assert_allclose(st["sumsq"], oracle64.row_sumsq64(X), rtol=2e-7)
+    np.testing.assert_allclose(st["dot"], oracle64.row_dot64(X, g), rtol=1e-5, atol=1e-9)
+    assert abs(st["g0_sumsq"] - float(np.dot(g.astype(np.float64), g.astype(np.float64)))) <= 2e-7 * st["g0_sumsq"]
+    assert np.array_equal(st["linf"], np.abs(X).max(axis=1))
+    rows = rng.permutation(n)[: max(1, n // 2)].astype(np.int32)
+    w1 = rng.uniform(0.1, 3, len(rows)).astype(np.float32)
+    w2 = rng.uniform(0.1, 3, len(rows)).astype(np.float32)
+    got = engine.row_combine(u, rows, w1, w2, 7.25).cpu().numpy()
+    assert np.array_equal(bits(got), bits(oracle64.combine_seq32(X, w1, w2, 7.25, rows=rows.tolist())))
+    u.close()
+
+
+@pytest.mark.parametrize("n,d,f", [(10, 421642, 2), (7, 1000, 1), (65, 3000, 10), (130, 2049, 20), (200, 777, 50)])
+def test_gram_distances_scores_vs_fp64(n, d, f):
+    from flagg import engine
+    rng = np.random.RandomState(d)
+    X = rows_model(rng, n, d, byz=f)
+    X[1] = X[0]                                                       # colluders: exact duplicate rows
+    u = engine.Updates(dev_lists(X))
+    G = engine.gram(u, center_row=0)
+    D, scores = engine.krum_scores(G, f)
+    D64 = oracle64.distances64(X)
+    assert D[0, 1] == 0.0 and np.all(np.diag(D) == 0) and np.array_equal(D, D.T)
+    mask = D64 > 0
+    assert np.max(np.abs(D[mask] - D64[mask]) / D64[mask]) <= 1e-5    # north_star: Gram-derived distances 1e-5
+    s64 = oracle64.krum_scores64(D64, f)
+    np.testing.assert_allclose(scores, s64, rtol=1e-5)
+    assert scores[0] == scores[1]
+    for mk in (1, max(2, n // 2)):
+        assert np.argsort(scores)[:mk].tolist() == np.argsort(s64)[:mk].tolist() or \
+            set(np.argsort(scores)[:mk].tolist()) == set(np.argsort(s64)[:mk].tolist())
+    u.close()
+
+
+def test_krum_selected_set_matches_reference_port_c1():
+    """BASELINE config 1 shape: 10 clients x SimpleCNN (421,642 params), Krum f=2."""
+    from src.defenses import KrumDefense
+    rng = np.random.RandomState(1)
+    seg = [288, 32, 18432, 64, 401408, 128, 1280, 10]
+    X = rows_model(rng, 10, sum(seg), byz=2)
+    for mk in (1, 5):
+        d = KrumDefense({"num_malicious": 2, "multi_k": mk})
+        res = d.aggregate(dev_lists(X, seg), [100] * 10)
+        ref = ref_port.krum(torch.from_numpy(X), 2, mk)
+        assert d.selected_clients == ref["selected"]
+        np.testing.assert_allclose(d.client_scores, ref["scores"], rtol=1e-5)
+        got = torch.cat([t.flatten().cpu() for t in res]).numpy()
+        assert np.array_equal(bits(got), bits(ref["out"].numpy()))
+
+
+def test_host_path_equals_device_path():
+    from flagg import MEDIAN, TRIMMED_MEAN, engine
+    rng = np.random.RandomState(5)
+    n, seg = 20, [70000, 333, 200000]
+    X = rows_model(rng, n, sum(seg), byz=4)
+    offs = np.concatenate([[0], np.cumsum(seg)]).astype(int)
+    host = [[torch.from_numpy(X[i, offs[p]:offs[p + 1]].copy()).pin_memory() for p in range(3)] for i in range(n)]
+    ud, uh = engine.Updates(dev_lists(X, seg)), engine.Updates(host)
+    for mode, k in ((MEDIAN, 0), (TRIMMED_MEAN, 2)):
+        a = engine.colwise_select(ud, mode, k).cpu().numpy()
+        b = engine.colwise_select(uh, mode, k)
+        assert not b.is_cuda and np.array_equal(bits(a), bits(b.numpy()))
+    ud.close()
+
+
+def test_errors_surface_as_exceptions():
+    from flagg import FlaggError, TRIMMED_MEAN, engine
+    from src.defenses import KrumDefense, get_defense
+    u = engine.Updates(dev_lists(np.zeros((4, 16), dtype=np.float32)))
+    with pytest.raises(FlaggError):
+        engine.colwise_select(u, TRIMMED_MEAN, 2)                     # n - 2k < 1
+    with pytest.raises(ValueError):
+        KrumDefense({"num_malicious": 2}).aggregate(dev_lists(np.zeros((3, 8), dtype=np.float32)), [1] * 3)
+    with pytest.raises(ValueError):
+        get_defense("nope", {})
+    u.close()
+
+
+# ---- full-size properties (BASELINE config 3: 100 x 25M, median, 10 GB) -----------------
+def test_full_size_median_properties():
+    from flagg import MEDIAN, engine
+    n, d = 100, 25_000_000
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    theta = torch.randn(d, device="cuda", generator=g) * 0.05
+    X = torch.empty((n, d), device="cuda")
+    for i in range(n):
+        X[i] = theta + torch.randn(d, device="cuda", generator=g) * (1e-2 if i < 10 else 1e-3)
+    del theta
+    u = engine.Updates([[X[i]] for i in range(n)])
+    out = engine.colwise_select(u, MEDIAN)
+    # (1) sampled columns against the oracle, bit-exact
+    cols = torch.randint(0, d, (50_000,), device="cuda", generator=g)
+    sub = X[:, cols].cpu().numpy()
+    assert np.array_equal(bits(out[cols].cpu().numpy()), bits(oracle64.median_stable(sub)))
+    # (2) rank property over ALL columns: #less <= r and #less_or_equal >= r+1
+    r = (n - 1) // 2
+    lt = torch.zeros(d, dtype=torch.int16, device="cuda")
+    le = torch.zeros(d, dtype=torch.int16, device="cuda")
+    for i in range(n):
+        lt += (X[i] < out)
+        le += (X[i] <= out)
+    assert bool((lt <= r).all()) and bool((le >= r + 1).all())
+    # (3) permutation invariance: client order does not change a tie-free median
+    perm = torch.randperm(n, generator=torch.Generator().manual_seed(1)).tolist()
+    u2 = engine.Updates([[X[i]] for i in perm])
+    out2 = engine.colwise_select(u2, MEDIAN)
+    assert torch.equal(out.view(torch.int32), out2.view(torch.int32))
+    u.close(); u2.close()

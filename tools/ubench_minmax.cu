@@ -1,0 +1,63 @@
+// Micro-benchmark: throughput of the compare-exchange building blocks on sm_100a.
+// Prints thread-ops per clock per SM for each variant (cycles from clock64 of one CTA).
+#include <cstdio>
+#include <cuda_runtime.h>
+#define ITERS 2048
+#define ILP 16
+template <int MODE>
+__global__ void __launch_bounds__(256) k(int* out, int seed, long long* cyc) {
+    int v[ILP], w[ILP];
+    for (int i = 0; i < ILP; ++i) { v[i] = seed * (threadIdx.x + 1) + i * 7919; w[i] = seed ^ (i * 104729 + threadIdx.x); }
+    long long t0 = clock64();
+#pragma unroll 1
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int i = 0; i < ILP; ++i) {
+            if (MODE == 0) {            // integer CE: min + max
+                int lo = min(v[i], w[i]), hi = max(v[i], w[i]); v[i] = lo + it; w[i] = hi;
+            } else if (MODE == 1) {     // float CE: fmin + fmax
+                float a = __int_as_float(v[i]), b = __int_as_float(w[i]);
+                float lo = fminf(a, b), hi = fmaxf(a, b); v[i] = __float_as_int(lo) + it; w[i] = __float_as_int(hi);
+            } else if (MODE == 2) {     // integer CE: min + (a+b-min)
+                int lo = min(v[i], w[i]); int hi = v[i] + w[i] - lo; v[i] = lo + it; w[i] = hi;
+            } else if (MODE == 3) {     // integer CE: min + xor trick
+                int lo = min(v[i], w[i]); int hi = v[i] ^ w[i] ^ lo; v[i] = lo + it; w[i] = hi;
+            } else if (MODE == 4) {     // 3-input min and max
+                int lo = min(min(v[i], w[i]), v[(i + 1) % ILP]); int hi = max(max(v[i], w[i]), v[(i + 1) % ILP]); v[i] = lo + it; w[i] = hi;
+            } else if (MODE == 5) {     // compare + two selects
+                bool p = v[i] > w[i]; int lo = p ? w[i] : v[i]; int hi = p ? v[i] : w[i]; v[i] = lo + it; w[i] = hi;
+            } else if (MODE == 6) {     // baseline: the "+ it" add alone (to subtract)
+                v[i] = v[i] + it; w[i] = w[i] ^ v[i];
+            } else if (MODE == 7) {     // pure FFMA (fma pipe reference)
+                float a = __int_as_float(v[i]), b = __int_as_float(w[i]);
+                a = fmaf(a, 1.0001f, b); b = fmaf(b, 0.9999f, a); v[i] = __float_as_int(a); w[i] = __float_as_int(b);
+            }
+        }
+    }
+    long long t1 = clock64();
+    int s = 0;
+    for (int i = 0; i < ILP; ++i) s ^= v[i] ^ w[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    if (threadIdx.x == 0 && blockIdx.x == 0) *cyc = t1 - t0;
+}
+template <int MODE> void run(const char* name, int ctas_per_sm) {
+    int sms; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    int grid = sms * ctas_per_sm; int* out; long long* cyc; long long h;
+    cudaMalloc(&out, grid * 256 * 4); cudaMalloc(&cyc, 8);
+    k<MODE><<<grid, 256>>>(out, 3, cyc); cudaDeviceSynchronize();
+    cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a); k<MODE><<<grid, 256>>>(out, 5, cyc); cudaEventRecord(b); cudaEventSynchronize(b);
+    float ms; cudaEventElapsedTime(&ms, a, b); cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
+    double items = double(ITERS) * ILP * 256 * ctas_per_sm;   // per SM
+    printf("%-34s ctas/SM=%d  %8.3f ms  cycles=%lld  items/clk/SM=%6.2f  (chip %7.1f G items/s)\n", name, ctas_per_sm, ms, h,
+           items / double(h), items * sms / (ms * 1e6));
+    cudaFree(out); cudaFree(cyc);
+}
+int main() {
+    for (int c : {2, 4}) {
+        run<0>("int CE  min+max", c); run<1>("f32 CE  fmin+fmax", c); run<2>("int CE  min + (a+b-min)", c);
+        run<3>("int CE  min + xor", c); run<4>("int min3+max3", c); run<5>("int cmp + 2 sel", c);
+        run<6>("baseline add+xor", c); run<7>("2 x FFMA", c);
+    }
+    return 0;
+}
