@@ -92,10 +92,11 @@ int flagg_colwise_select(const flagg_view* v, int mode, int k, float* out, void*
  *   dot[i]   = sum_c x_ic*g0_c (FP64)-- torch.dot at fltrust.py:174 (needs g0)
  *   linf[i]  = max_c |x_ic|          -- differential_privacy.py:230
  *   g0_sumsq = sum_c g0_c^2          -- fltrust.py:176,209
- * g0: device fp32 [d] (segments concatenated) or NULL.  Deterministic (fixed
- * reduction order). */
-int flagg_row_reduce(const flagg_view* v, const float* g0, double* sumsq, double* dot,
-                     float* linf, double* g0_sumsq, void* stream);
+ * g0: device fp32 [d] (segments concatenated) or NULL.  centered != 0: the per-client
+ * statistics are those of (x_i - g0) instead of x_i -- ||x_i - g0||^2 is the Weiszfeld
+ * distance of trimmed_mean.py:245.  Deterministic (fixed reduction order). */
+int flagg_row_reduce(const flagg_view* v, const float* g0, int centered, double* sumsq,
+                     double* dot, float* linf, double* g0_sumsq, void* stream);
 
 /* ---- K3: weighted row combination ------------------------------------------ */
 /* out[c] = ( ...((0 + t_0) + t_1) ... + t_{m-1}) / divisor,
@@ -110,14 +111,15 @@ int flagg_row_combine(const flagg_view* v, int m, const int32_t* rows, const flo
                       const float* w2, float divisor, float* out, void* stream);
 
 /* ---- K4/K5: Krum ------------------------------------------------------------ */
-/* G (device, FP64, n*n row-major, symmetric) = (X - c)(X - c)^T where c is row
- * `center_row` of X (0 <= center_row < n; pairwise distances are translation
- * invariant, centring removes the common component of full-weight rows)
- * or no centring if center_row < 0.  Replaces the O(n^2) loop of
+/* G (device, FP64, n*n row-major, symmetric) = (X - c)(X - c)^T where c = `center`
+ * (device fp32 [d], segments concatenated; NULL = no centring).  Pairwise distances
+ * are translation invariant; centring on a vector inside the benign cluster removes
+ * the common component of full-weight rows so fp32 products keep 1e-5 on the
+ * distances (DESIGN.md "Gram precision").  Replaces the O(n^2) loop of
  * torch.norm(fi - fj) at krum.py:92-97.  With the parameter dimension sharded,
  * partial G's add: all-reduce them before flagg_krum_scores.
  * `accumulate` != 0 adds into G instead of overwriting it. */
-int flagg_gram(const flagg_view* v, int center_row, int accumulate, double* G, void* stream);
+int flagg_gram(const flagg_view* v, const float* center, int accumulate, double* G, void* stream);
 
 /* D[i,j] = sqrt(max(0, G_ii + G_jj - 2 G_ij)) (un-squared, as krum.py:95), D_ii = 0;
  * scores[i] = sum of the (n-f-2) smallest D[i,j], j != i (krum.py:122-129).

@@ -6,8 +6,8 @@
 // np.sort / np.sum at krum.py:122-129.
 //
 // Precision: rows are full weight vectors, so ||x||^2 >> ||x_i - x_j||^2.
-// Every element is centred on a common row before it is multiplied (distances are
-// translation invariant), products are accumulated in fp32 for at most 1024 columns and
+// Every element is centred on a common vector c before it is multiplied (distances are
+// translation invariant; the caller passes a robust centre, see flagg.engine.gram), products are accumulated in fp32 for at most 1024 columns and
 // then folded into FP64; D^2 and sqrt are formed in FP64.
 //
 // This file is the CUDA-core (FFMA) implementation: 64x64 output tiles, split-K across
@@ -25,6 +25,7 @@ constexpr int G_FLUSH_UNITS = 8;  // fold fp32 -> fp64 every 8 x 128 columns
 // Stage GK columns of rows [r0, r0+64) into sm[k][row] (centred, zero padded).
 __device__ __forceinline__ void gram_stage(const ViewDev& v, int p, int64_t col0, int valid, int r0,
                                            const float* __restrict__ crow, float (*sm)[GT + 1]) {
+    // crow: centre values of this segment (already offset to the segment start) or NULL
     const int tid = threadIdx.x, kcol = tid & 31, rsub = tid >> 5;
     const bool ok = kcol < valid;
     const float cval = (ok && crow) ? __ldg(crow + col0 + kcol) : 0.f;
@@ -40,7 +41,7 @@ __device__ __forceinline__ void gram_stage(const ViewDev& v, int p, int64_t col0
 // grid = (tiles, splits).  Tile t -> (bi <= bj).  Split s owns 128-column units
 // [s*upb, (s+1)*upb).  Writes its 64x64 FP64 partial to part[(s*tiles + t)*4096 ...].
 __global__ void __launch_bounds__(G_THREADS)
-gram_ffma_kernel(ViewDev v, int center_row, int nb, int64_t total_units, int64_t units_per_split,
+gram_ffma_kernel(ViewDev v, const float* __restrict__ center, int nb, int64_t total_units, int64_t units_per_split,
                  double* __restrict__ part) {
     __shared__ float As[GK][GT + 1];
     __shared__ float Bs[GK][GT + 1];
@@ -66,7 +67,7 @@ gram_ffma_kernel(ViewDev v, int center_row, int nb, int64_t total_units, int64_t
         const int p = find_segment(ustart, v.P, u);
         const int64_t c0 = (u - ustart[p]) * 128;
         const int len = int(min((long long)(128), (long long)v.seg_start[p + 1] - v.seg_start[p] - c0));
-        const float* crow = center_row >= 0 ? v.seg_ptrs[size_t(center_row) * v.P + p] : nullptr;
+        const float* crow = center ? center + v.seg_start[p] : nullptr;
         for (int ks = 0; ks < len; ks += GK) {
             __syncthreads();
             gram_stage(v, p, c0 + ks, len - ks, bi * GT, crow, As);
@@ -172,11 +173,10 @@ using namespace flagg;
 
 extern "C" {
 
-int flagg_gram(const flagg_view* cv, int center_row, int accumulate, double* G, void* stream) {
+int flagg_gram(const flagg_view* cv, const float* center, int accumulate, double* G, void* stream) {
     FLAGG_REQUIRE(cv && G, "flagg_gram: NULL argument");
     flagg_view* v = const_cast<flagg_view*>(cv);
     const int n = v->dev.n;
-    FLAGG_REQUIRE(center_row < n, "flagg_gram: center_row %d out of range (n=%d)", center_row, n);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int nb = (n + GT - 1) / GT;
     const int tiles = nb * (nb + 1) / 2;
@@ -196,7 +196,7 @@ int flagg_gram(const flagg_view* cv, int center_row, int accumulate, double* G, 
     if (rc != FLAGG_OK) return rc;
     double* part = static_cast<double*>(v->d_scratch);
     dim3 grid(tiles, unsigned(splits));
-    gram_ffma_kernel<<<grid, G_THREADS, 0, st>>>(v->dev, center_row, nb, units, upb, part);
+    gram_ffma_kernel<<<grid, G_THREADS, 0, st>>>(v->dev, center, nb, units, upb, part);
     FLAGG_CUDA(cudaGetLastError());
     gram_reduce_kernel<<<tiles, 256, 0, st>>>(part, tiles, int(splits), nb, n, accumulate, G);
     FLAGG_CUDA(cudaGetLastError());

@@ -32,7 +32,7 @@ __device__ __forceinline__ float warp_max(float v) {
 // total lands in the CTA's shared per-row accumulator (one owner warp per row: no
 // atomics).  Per-CTA partials go to `part`; row_reduce_finalize adds them in CTA order,
 // so the result is deterministic.
-template <bool VEC4, bool HAS_G0>
+template <bool VEC4, bool HAS_G0, bool CENTERED>
 __global__ void __launch_bounds__(RR_THREADS)
 row_reduce_kernel(ViewDev v, const float* __restrict__ g0, double* __restrict__ part_ss,
                   double* __restrict__ part_dot, float* __restrict__ part_linf,
@@ -82,17 +82,19 @@ row_reduce_kernel(ViewDev v, const float* __restrict__ g0, double* __restrict__ 
 #pragma unroll
                 for (int jj = 0; jj < 16; ++jj) {
                     const int j = lane + 32 * jj;
-                    const float4 a = x[jj];
+                    float4 a = x[jj];
+                    const float4 g = HAS_G0 ? g4[j & (RR_CHUNK / 4 - 1)] : make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (CENTERED && j < nv) { a.x -= g.x; a.y -= g.y; a.z -= g.z; a.w -= g.w; }
                     ss += double((a.x * a.x + a.y * a.y) + (a.z * a.z + a.w * a.w));
                     mx = fmaxf(fmaxf(mx, fmaxf(fabsf(a.x), fabsf(a.y))), fmaxf(fabsf(a.z), fabsf(a.w)));
                     if (HAS_G0) {
-                        const float4 g = g4[j & (RR_CHUNK / 4 - 1)];
                         dt += double((a.x * g.x + a.y * g.y) + (a.z * g.z + a.w * g.w));
                     }
                 }
             }
             for (int j = (nv << 2) + lane; j < len; j += 32) {   // tail / unaligned path
-                const float a = ldg_stream(row + j);
+                float a = ldg_stream(row + j);
+                if (CENTERED) a -= g0s[j];
                 ss += double(a * a);
                 mx = fmaxf(mx, fabsf(a));
                 if (HAS_G0) dt += double(a * g0s[j]);
@@ -230,11 +232,12 @@ using namespace flagg;
 
 extern "C" {
 
-int flagg_row_reduce(const flagg_view* cv, const float* g0, double* sumsq, double* dot, float* linf,
+int flagg_row_reduce(const flagg_view* cv, const float* g0, int centered, double* sumsq, double* dot, float* linf,
                      double* g0_sumsq, void* stream) {
     FLAGG_REQUIRE(cv, "flagg_row_reduce: NULL view");
     FLAGG_REQUIRE(!(dot && !g0), "flagg_row_reduce: dot requested without g0");
     FLAGG_REQUIRE(!(g0_sumsq && !g0), "flagg_row_reduce: g0_sumsq requested without g0");
+    FLAGG_REQUIRE(!(centered && !g0), "flagg_row_reduce: centered statistics need g0");
     flagg_view* v = const_cast<flagg_view*>(cv);
     const int n = v->dev.n;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -259,10 +262,12 @@ int flagg_row_reduce(const flagg_view* cv, const float* g0, double* sumsq, doubl
         FLAGG_CUDA(cudaGetLastError());
         return FLAGG_OK;
     };
-    if (vec4 && g0) rc = launch(row_reduce_kernel<true, true>);
-    else if (vec4) rc = launch(row_reduce_kernel<true, false>);
-    else if (g0) rc = launch(row_reduce_kernel<false, true>);
-    else rc = launch(row_reduce_kernel<false, false>);
+    if (vec4 && g0 && centered) rc = launch(row_reduce_kernel<true, true, true>);
+    else if (g0 && centered) rc = launch(row_reduce_kernel<false, true, true>);
+    else if (vec4 && g0) rc = launch(row_reduce_kernel<true, true, false>);
+    else if (vec4) rc = launch(row_reduce_kernel<true, false, false>);
+    else if (g0) rc = launch(row_reduce_kernel<false, true, false>);
+    else rc = launch(row_reduce_kernel<false, false, false>);
     if (rc != FLAGG_OK) return rc;
     row_reduce_finalize<<<(n + 127) / 128, 128, 0, st>>>(part_ss, part_dot, part_linf, part_g0, nblocks, n,
                                                          sumsq, dot, linf, g0_sumsq);

@@ -39,9 +39,9 @@ def lib():
         "flagg_view_cols": (i64, [vp]),
         "flagg_view_rows": (i32, [vp]),
         "flagg_colwise_select": (i32, [vp, i32, i32, vp, vp]),
-        "flagg_row_reduce": (i32, [vp, vp, vp, vp, vp, vp, vp]),
+        "flagg_row_reduce": (i32, [vp, vp, i32, vp, vp, vp, vp, vp]),
         "flagg_row_combine": (i32, [vp, i32, C.POINTER(C.c_int32), C.POINTER(f32), C.POINTER(f32), f32, vp, vp]),
-        "flagg_gram": (i32, [vp, i32, i32, vp, vp]),
+        "flagg_gram": (i32, [vp, vp, i32, vp, vp]),
         "flagg_krum_scores": (i32, [vp, i32, i32, vp, vp, vp]),
         "flagg_colwise_select_host": (i32, [i32, i32, C.POINTER(i64), C.POINTER(vp), i32, i32, vp, i64]),
         "flagg_upload_rows": (i32, [i32, i32, C.POINTER(i64), C.POINTER(vp), vp, i64, vp]),

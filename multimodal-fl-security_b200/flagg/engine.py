@@ -152,8 +152,9 @@ def colwise_select(u: Updates, mode: int, k: int = 0) -> torch.Tensor:
     return out
 
 
-def row_stats(u: Updates, g0_flat: Optional[torch.Tensor] = None, group=None) -> dict:
-    """K2.  One pass over X: per-client sum of squares, dot with g0 (FP64) and max |x|.
+def row_stats(u: Updates, g0_flat: Optional[torch.Tensor] = None, group=None, centered: bool = False) -> dict:
+    """K2.  One pass over X: per-client sum of squares, dot with g0 (FP64) and max |x|
+    (of x - g0 when ``centered``).
     With ``group`` (a torch.distributed process group; X sharded by parameters) the
     partial sums are all-reduced so every rank gets whole-vector statistics."""
     u = u.resident()
@@ -168,7 +169,7 @@ def row_stats(u: Updates, g0_flat: Optional[torch.Tensor] = None, group=None) ->
                 raise ValueError("g0 has the wrong number of elements")
             g_ptr = g0_flat.data_ptr()
         p = buf.data_ptr()
-        check(lib().flagg_row_reduce(u.view(), g_ptr, p, (p + 8 * n) if g_ptr else None, linf.data_ptr(),
+        check(lib().flagg_row_reduce(u.view(), g_ptr, 1 if centered else 0, p, (p + 8 * n) if g_ptr else None, linf.data_ptr(),
                                      (p + 16 * n) if g_ptr else None, _stream()), "flagg_row_reduce")
         if group is not None:
             import torch.distributed as dist
@@ -201,13 +202,37 @@ def row_combine(u: Updates, rows, w1, w2, divisor: float) -> torch.Tensor:
     return out
 
 
-def gram(u: Updates, center_row: int = 0, group=None) -> torch.Tensor:
+CENTER_ROWS = 31   # rows whose coordinate-wise median centres the Gram matrix
+
+
+def robust_center(u: Updates) -> torch.Tensor:
+    """A vector inside the benign cluster: the coordinate-wise median (K1) of up to 31
+    evenly spaced clients.  It only conditions the Gram arithmetic (distances are
+    translation invariant), so it need not be exact or agreed between ranks: with the
+    parameter dimension sharded every rank centres its own columns."""
+    u = u.resident()
+    idx = sorted(set(int(round(x)) for x in np.linspace(0, u.n - 1, min(u.n, CENTER_ROWS))))
+    sub = Updates([u.rows[i] for i in idx])
+    c = colwise_select(sub, MEDIAN)
+    sub.close()
+    return c
+
+
+def gram(u: Updates, center: Optional[torch.Tensor] = None, group=None, auto_center: bool = True) -> torch.Tensor:
     """K4.  FP64 centred Gram matrix [n, n] on the device; all-reduced over ``group``
-    when the parameter dimension is sharded (partial Grams add)."""
+    when the parameter dimension is sharded (partial Grams add).  ``center``: flat fp32
+    [d] on the device; by default ``robust_center(u)``."""
     u = u.resident()
     with torch.cuda.device(u.device):
+        if center is None and auto_center:
+            center = robust_center(u)
+        if center is not None:
+            center = center.to(device=u.device, dtype=torch.float32).contiguous()
+            if center.numel() != u.d:
+                raise ValueError("center has the wrong number of elements")
         G = torch.empty((u.n, u.n), dtype=torch.float64, device=u.device)
-        check(lib().flagg_gram(u.view(), center_row, 0, G.data_ptr(), _stream()), "flagg_gram")
+        check(lib().flagg_gram(u.view(), center.data_ptr() if center is not None else None, 0, G.data_ptr(),
+                               _stream()), "flagg_gram")
         if group is not None:
             import torch.distributed as dist
             dist.all_reduce(G, op=dist.ReduceOp.SUM, group=group)

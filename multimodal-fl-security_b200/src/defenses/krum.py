@@ -28,13 +28,13 @@ class KrumDefense(BaseDefense):
         return torch.cat([t.flatten().float() for t in update])
 
     def _distances_and_scores(self, u: engine.Updates, f: int):
-        G = engine.gram(u, center_row=0, group=self._group)
+        G = engine.gram(u, group=self._group)
         return engine.krum_scores(G, f, want_D=True)
 
     def _compute_distances(self, client_updates) -> np.ndarray:
         """Pairwise L2 distance matrix, float64 [n, n] (krum.py:73-99)."""
         u = engine.Updates(client_updates)
-        G = engine.gram(u, center_row=0, group=self._group)
+        G = engine.gram(u, group=self._group)
         n = u.n
         D, _ = engine.krum_scores(G, max(0, n - 3), want_D=True) if n >= 3 else (self._tiny_D(G), None)
         return D

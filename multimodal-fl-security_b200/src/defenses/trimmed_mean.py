@@ -74,19 +74,15 @@ class GeometricMedianDefense(BaseDefense):
         n = u.n
         current = engine.colwise_select(u, MEDIAN)                       # :240
         for iteration in range(self.max_iters):
-            # ||u_i - x||^2 = ||u_i||^2 - 2 u_i.x + ||x||^2 would cancel badly; use the
-            # centred Gram row instead: append x as an extra "client" and centre on it.
-            ext = engine.Updates([row for row in u.rows] + [[current]] if u.P == 1 else
-                                 [row for row in u.rows] + [u.split(current, to_host=False)])
-            G = engine.gram(ext, center_row=n, group=self._group)
-            dist = torch.sqrt(torch.clamp(torch.diagonal(G)[:n], min=0.0)).to(torch.float32)
+            # ||u_i - x|| for every client in one pass (K2, centred statistics), :245
+            st = engine.row_stats(u, current, group=self._group, centered=True)
+            dist = torch.from_numpy(np.sqrt(st['sumsq']).astype(np.float32))
             dist = torch.clamp(dist, min=1e-10)                          # :248
             w = (1.0 / dist)                                             # :251
             wsum = w.sum()
-            new = engine.row_combine(u, list(range(n)), w.cpu().numpy(), None, float(wsum))
+            new = engine.row_combine(u, list(range(n)), w.numpy(), None, float(wsum))
             change = torch.norm(new - current)
             current = new
-            ext.close()
             if change < self.tolerance:                                  # :258-260
                 self.num_iters = iteration + 1
                 break

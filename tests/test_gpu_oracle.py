@@ -153,7 +153,7 @@ def test_gram_distances_scores_vs_fp64(n, d, f):
     X = rows_model(rng, n, d, byz=f)
     X[1] = X[0]                                                       # colluders: exact duplicate rows
     u = engine.Updates(dev_lists(X))
-    G = engine.gram(u, center_row=0)
+    G = engine.gram(u)
     D, scores = engine.krum_scores(G, f)
     D64 = oracle64.distances64(X)
     assert D[0, 1] == 0.0 and np.all(np.diag(D) == 0) and np.array_equal(D, D.T)

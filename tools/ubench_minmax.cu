@@ -5,7 +5,7 @@
 #define ITERS 2048
 #define ILP 16
 template <int MODE>
-__global__ void __launch_bounds__(256) k(int* out, int seed, long long* cyc) {
+__global__ void __launch_bounds__(256) k(int* out, int seed, long long* cyc, int one, int mone) {
     int v[ILP], w[ILP];
     for (int i = 0; i < ILP; ++i) { v[i] = seed * (threadIdx.x + 1) + i * 7919; w[i] = seed ^ (i * 104729 + threadIdx.x); }
     long long t0 = clock64();
@@ -28,6 +28,36 @@ __global__ void __launch_bounds__(256) k(int* out, int seed, long long* cyc) {
                 bool p = v[i] > w[i]; int lo = p ? w[i] : v[i]; int hi = p ? v[i] : w[i]; v[i] = lo + it; w[i] = hi;
             } else if (MODE == 6) {     // baseline: the "+ it" add alone (to subtract)
                 v[i] = v[i] + it; w[i] = w[i] ^ v[i];
+            } else if (MODE == 8) {     // f32 min + hi via two runtime-multiplier IMADs on the bit patterns
+                float lo = fminf(__int_as_float(v[i]), __int_as_float(w[i])); int t, hi;
+                asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(t) : "r"(v[i]), "r"(one), "r"(w[i]));
+                asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(hi) : "r"(__float_as_int(lo)), "r"(mone), "r"(t));
+                v[i] = __float_as_int(lo) + it; w[i] = hi;
+            } else if (MODE == 9) {     // IMAD alone (two per item)
+                int t, hi;
+                asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(t) : "r"(v[i]), "r"(one), "r"(w[i]));
+                asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(hi) : "r"(w[i]), "r"(mone), "r"(t));
+                v[i] = t; w[i] = hi;
+            } else if (MODE == 10) {    // 1/3 min+max, 2/3 min+2xIMAD
+                float a = __int_as_float(v[i]), b = __int_as_float(w[i]);
+                float lo = fminf(a, b); int hi;
+                if (i % 3 == 0) { hi = __float_as_int(fmaxf(a, b)); }
+                else { int t; asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(t) : "r"(v[i]), "r"(one), "r"(w[i]));
+                       asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(hi) : "r"(__float_as_int(lo)), "r"(mone), "r"(t)); }
+                v[i] = __float_as_int(lo) + it; w[i] = hi;
+            } else if (MODE == 11) {    // 1/2 min+max, 1/2 min+2xIMAD
+                float a = __int_as_float(v[i]), b = __int_as_float(w[i]);
+                float lo = fminf(a, b); int hi;
+                if (i % 2 == 0) { hi = __float_as_int(fmaxf(a, b)); }
+                else { int t; asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(t) : "r"(v[i]), "r"(one), "r"(w[i]));
+                       asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(hi) : "r"(__float_as_int(lo)), "r"(mone), "r"(t)); }
+                v[i] = __float_as_int(lo) + it; w[i] = hi;
+            } else if (MODE == 12) {    // pure min+max, no extra add (network-like): values recirculate
+                int lo = min(v[i], w[i]), hi = max(v[i], w[i]); v[i] = hi; w[(i + 1) % ILP] = lo;
+            } else if (MODE == 13) {    // f32 min + predicated-select hi on fma pipe: hi = a + b - lo in FLOAT for compare only
+                float a = __int_as_float(v[i]), b = __int_as_float(w[i]);
+                float lo = fminf(a, b); float hi = fmaf(a, 1.0f, b) - lo;   // (inexact; throughput probe only)
+                v[i] = __float_as_int(lo) + it; w[i] = __float_as_int(hi);
             } else if (MODE == 7) {     // pure FFMA (fma pipe reference)
                 float a = __int_as_float(v[i]), b = __int_as_float(w[i]);
                 a = fmaf(a, 1.0001f, b); b = fmaf(b, 0.9999f, a); v[i] = __float_as_int(a); w[i] = __float_as_int(b);
@@ -44,9 +74,9 @@ template <int MODE> void run(const char* name, int ctas_per_sm) {
     int sms; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
     int grid = sms * ctas_per_sm; int* out; long long* cyc; long long h;
     cudaMalloc(&out, grid * 256 * 4); cudaMalloc(&cyc, 8);
-    k<MODE><<<grid, 256>>>(out, 3, cyc); cudaDeviceSynchronize();
+    k<MODE><<<grid, 256>>>(out, 3, cyc, 1, -1); cudaDeviceSynchronize();
     cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
-    cudaEventRecord(a); k<MODE><<<grid, 256>>>(out, 5, cyc); cudaEventRecord(b); cudaEventSynchronize(b);
+    cudaEventRecord(a); k<MODE><<<grid, 256>>>(out, 5, cyc, 1, -1); cudaEventRecord(b); cudaEventSynchronize(b);
     float ms; cudaEventElapsedTime(&ms, a, b); cudaMemcpy(&h, cyc, 8, cudaMemcpyDeviceToHost);
     double items = double(ITERS) * ILP * 256 * ctas_per_sm;   // per SM
     printf("%-34s ctas/SM=%d  %8.3f ms  cycles=%lld  items/clk/SM=%6.2f  (chip %7.1f G items/s)\n", name, ctas_per_sm, ms, h,
@@ -58,6 +88,8 @@ int main() {
         run<0>("int CE  min+max", c); run<1>("f32 CE  fmin+fmax", c); run<2>("int CE  min + (a+b-min)", c);
         run<3>("int CE  min + xor", c); run<4>("int min3+max3", c); run<5>("int cmp + 2 sel", c);
         run<6>("baseline add+xor", c); run<7>("2 x FFMA", c);
+        run<8>("f32 min + 2 IMAD", c); run<9>("2 IMAD", c); run<10>("mix 1/3 minmax 2/3 min+2IMAD", c);
+        run<11>("mix 1/2 minmax 1/2 min+2IMAD", c); run<12>("int min+max only", c); run<13>("f32 min + FFMA + FADD", c);
     }
     return 0;
 }
