@@ -89,7 +89,7 @@ colselect_radix_kernel(ViewDev v, int mode, int k, float* __restrict__ out, int6
             const int kk = int(uk ^ 0x80000000u);
             bool has_nan = false;
             for (int i = 0; i < n; ++i) { const float x = sptr[i][c]; has_nan |= (x != x); }
-            if (has_nan || kk == 0 || kk == -1) res = median_slow(sptr, n, c, has_nan, res);
+            if (has_nan || kk == 0 || kk == -1) res = median_slow(sptr, n, c, res);
         } else {
             const unsigned uL = radix_select(sptr, n, c, k, hist);
             const unsigned uH = radix_select(sptr, n, c, n - k - 1, hist);
@@ -141,8 +141,7 @@ extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float*
             if (cand.n >= n) { e = &cand; break; }
         FLAGG_REQUIRE(e, "flagg_colwise_select: no network for n=%d", n);
         const int variant = (mode == FLAGG_TRIMMED_MEAN) ? CS_TRIMMED_ANY : (e->n == n ? CS_MEDIAN_EXACT : CS_MEDIAN_ANY);
-        const int grid = int(std::min<int64_t>(units, int64_t(sms) * 16));
-        return e->fn(v->dev, variant, k, out, units, grid, st);
+        return e->fn(v->dev, variant, k, out, units, sms, st);
     }
     const size_t smem = sizeof(float*) * size_t(n) + sizeof(int) * 16 * RX_THREADS;
     FLAGG_REQUIRE(smem <= 200 * 1024, "flagg_colwise_select: n=%d too large", n);
