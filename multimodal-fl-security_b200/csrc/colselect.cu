@@ -8,7 +8,7 @@
 // 17 for a trimmed mean -- so this path is a correctness fallback, not a roofline
 // kernel (DESIGN.md says so); every load is still a full coalesced 128-byte line.
 #include "colselect_net.cuh"
-#include "gen/network_sizes.h"
+#include "network_sizes.h"
 
 namespace flagg {
 
