@@ -41,6 +41,25 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def tf32_peak_tflops():
+    """Dense TF32 GEMM rate of this GPU (library GEMM, used only as the roofline denominator)."""
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    a = torch.randn(8192, 8192, device="cuda")
+    b = torch.randn(8192, 8192, device="cuda")
+    best = float("inf")
+    for _ in range(10):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    torch.backends.cuda.matmul.allow_tf32 = old
+    del a, b
+    return 2.0 * 8192 ** 3 / best / 1e9
+
+
 def ncu_traffic(kernel_key):
     """dram bytes per launch from the committed ncu capture, if one exists."""
     p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
@@ -196,9 +215,15 @@ def extra_defenses(rank, world, dist_on, group):
             G = engine.gram(u, group=group)         # K4 (+ all-reduce of the n x n FP64 Gram)
             engine.krum_scores(G, 100, want_D=False)              # K5
         return step
-    bench("multikrum_gram_C4shard_1000x3.125M_f100", n4, d4, krum_factory, 4.0 * n4 * d4, steps=1)
-    out["multikrum_gram_C4shard_1000x3.125M_f100"]["TFLOPs_alg"] = \
-        world * n4 * (n4 + 1) * d4 / (out["multikrum_gram_C4shard_1000x3.125M_f100"]["ms"] / 1e3) / 1e12
+    bench("multikrum_gram_C4shard_1000x3.125M_f100", n4, d4, krum_factory, 4.0 * n4 * d4, steps=3)
+    gk = out["multikrum_gram_C4shard_1000x3.125M_f100"]
+    # tensor roofline of the Gram kernel: algorithmic flops n(n+1)d (unique pairs, mul+add) against
+    # exact-FP32-by-3xTF32 peak = measured dense TF32 GEMM rate / 3 (cuBLAS 8192^3, best of 10, same process)
+    tf32 = tf32_peak_tflops()
+    gk["TFLOPs_alg"] = world * n4 * (n4 + 1) * d4 / (gk["ms"] / 1e3) / 1e12
+    gk["roofline"] = {"bound": "tensor", "achieved": gk["TFLOPs_alg"] / world, "peak": tf32 / 3.0, "unit": "TFLOP/s",
+                      "frac": gk["TFLOPs_alg"] / world / (tf32 / 3.0), "tf32_dense_measured": tf32,
+                      "kernel": "gram_tc_kernel (tcgen05 kind::tf32, 3 products per k-step)"}
     return out
 
 

@@ -13,9 +13,14 @@
 // This file is the CUDA-core (FFMA) implementation: 64x64 output tiles, split-K across
 // the grid with a deterministic two-stage reduction.  gram_tc.cu (3xTF32 on tcgen05) is
 // the tensor-core path for large n.
+#include <cstdlib>
+#include <cstring>
+
 #include "common.cuh"
 
 namespace flagg {
+
+int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st);  // gram_tc.cu
 
 constexpr int GT = 64;          // output tile edge
 constexpr int GK = 32;          // columns per k-step (128 B of every row)
@@ -178,6 +183,16 @@ int flagg_gram(const flagg_view* cv, const float* center, int accumulate, double
     flagg_view* v = const_cast<flagg_view*>(cv);
     const int n = v->dev.n;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    {   // tensor-core path (gram_tc.cu) for n >= 64 on 16-byte aligned tensors; FLAGG_GRAM_IMPL=ffma|tc overrides
+        const char* impl = getenv("FLAGG_GRAM_IMPL");
+        const bool force_tc = impl && !strcmp(impl, "tc"), force_ffma = impl && !strcmp(impl, "ffma");
+        if (force_tc && v->align_bytes < 16) {
+            set_error("flagg_gram: FLAGG_GRAM_IMPL=tc needs 16-byte aligned tensors");
+            return FLAGG_EUNSUPPORTED;
+        }
+        if (v->total_units[GRAN_128] > 0 && v->align_bytes >= 16 && !force_ffma && (n >= 64 || force_tc))
+            return gram_tc_launch(v, center, accumulate, G, st);
+    }
     const int nb = (n + GT - 1) / GT;
     const int tiles = nb * (nb + 1) / 2;
     const int64_t units = v->total_units[GRAN_128];

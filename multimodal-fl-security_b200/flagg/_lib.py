@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libflagg.so")
+LIB_PATH = os.environ.get("FLAGG_LIB") or os.path.join(_HERE, "libflagg.so")   # FLAGG_LIB: tuning builds only
 
 MEDIAN, TRIMMED_MEAN = 0, 1
 

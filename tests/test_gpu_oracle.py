@@ -168,6 +168,58 @@ def test_gram_distances_scores_vs_fp64(n, d, f):
     u.close()
 
 
+@pytest.mark.parametrize("impl", ["tc", "ffma"])
+@pytest.mark.parametrize("n,seg,f", [(64, [4096], 10), (128, [32], 20), (65, [3000], 10), (130, [2048, 1], 20),
+                                     (200, [780, 64, 5000], 50), (257, [33, 95, 4100], 60), (1000, [7000, 36, 3000], 100)])
+def test_gram_paths_vs_fp64(n, seg, f, impl, monkeypatch):
+    """K4 on the tensor cores (tcgen05 3xTF32, gram_tc.cu) and on the CUDA cores (gram.cu), forced
+    through FLAGG_GRAM_IMPL, against FP64: distances within 1e-5 relative (north_star), exact
+    symmetry, zero distance between exact duplicates, identical Krum selection.  Ragged segment
+    lengths exercise zero-padded k-blocks and row tiles beyond n."""
+    from flagg import engine
+    monkeypatch.setenv("FLAGG_GRAM_IMPL", impl)
+    d = sum(seg)
+    rng = np.random.RandomState(n + d)
+    X = rows_model(rng, n, d, byz=f)
+    X[1] = X[0]
+    u = engine.Updates(dev_lists(X, seg))
+    G = engine.gram(u)
+    D, scores = engine.krum_scores(G, f)
+    D64 = oracle64.distances64(X)
+    assert D[0, 1] == 0.0 and np.all(np.diag(D) == 0) and np.array_equal(D, D.T)
+    mask = D64 > 0
+    assert np.max(np.abs(D[mask] - D64[mask]) / D64[mask]) <= 1e-5    # tolerance stated by north_star
+    s64 = oracle64.krum_scores64(D64, f)
+    np.testing.assert_allclose(scores, s64, rtol=1e-5)
+    for mk in (1, max(2, n // 2)):
+        assert set(np.argsort(scores)[:mk].tolist()) == set(np.argsort(s64)[:mk].tolist())
+    u.close()
+
+
+def test_gram_tc_is_default_for_large_n_and_falls_back_when_unaligned(monkeypatch):
+    """n >= 64 on 16-byte aligned tensors takes the tensor-core path; rows that are 4-byte
+    aligned views take the CUDA-core path; both agree to 1e-5 on every distance."""
+    from flagg import engine
+    monkeypatch.delenv("FLAGG_GRAM_IMPL", raising=False)
+    rng = np.random.RandomState(3)
+    n, d = 96, 5001
+    X = rows_model(rng, n, d, byz=9)
+    big = torch.from_numpy(X).cuda()                                   # row stride 5001 floats: rows 4-byte aligned only
+    u_unal = engine.Updates([[big[i]] for i in range(n)])
+    u_al = engine.Updates(dev_lists(X))
+    c = torch.from_numpy(np.median(X[::4], axis=0)).cuda()
+    Ga, Gu = engine.gram(u_al, center=c).cpu().numpy(), engine.gram(u_unal, center=c).cpu().numpy()
+    Xc = X.astype(np.float64) - c.cpu().numpy().astype(np.float64)
+    G64 = Xc @ Xc.T
+    scale = np.sqrt(np.outer(np.diag(G64), np.diag(G64)))
+    assert np.max(np.abs(Ga - G64) / scale) <= 1e-5 and np.max(np.abs(Gu - G64) / scale) <= 1e-6
+    assert not np.array_equal(Ga, Gu)                                  # different arithmetic => different paths ran
+    monkeypatch.setenv("FLAGG_GRAM_IMPL", "tc")
+    with pytest.raises(engine.FlaggError):
+        engine.gram(u_unal, center=c)
+    u_al.close(); u_unal.close()
+
+
 def test_krum_selected_set_matches_reference_port_c1():
     """BASELINE config 1 shape: 10 clients x SimpleCNN (421,642 params), Krum f=2."""
     from src.defenses import KrumDefense
