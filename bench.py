@@ -173,7 +173,7 @@ def run_reference(args, rank):
         "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def extra_defenses(rank, world, dist_on, group):
@@ -311,10 +311,31 @@ def run_flagg(args, rank, world, local_rank):
             line["cpu_baseline"] = {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port",
                                     "sample": f"{n} clients x {CPU_SAMPLE_COLS} of {d} columns, 1 step after 1 warm-up "
                                               f"(oracle port of torch.stack+torch.median, {dt:.2f} s/step)"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist_on:
         dist.barrier()
         dist.destroy_process_group()
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL's version banner) print to fd 1; the contract is ONE JSON line on stdout.
+    Everything else is sent to stderr and the line is written to the saved descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
@@ -330,6 +351,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    quiet_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "flagg" else args.warmup
     if args.impl == "reference":
         run_reference(args, rank)
