@@ -136,11 +136,18 @@ extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float*
         return FLAGG_OK;
     }
     if (n <= FLAGG_NET_MAX) {
+        for (int64_t len : v->seg_numel)
+            if (len >= (int64_t(1) << 30)) {
+                set_error("flagg_colwise_select: a tensor of %lld elements exceeds the 2^30-element limit of the network path", (long long)len);
+                return FLAGG_EUNSUPPORTED;
+            }
         const NetEntry* e = nullptr;
         for (const NetEntry& cand : g_nets)
             if (cand.n >= n) { e = &cand; break; }
         FLAGG_REQUIRE(e, "flagg_colwise_select: no network for n=%d", n);
-        const int variant = (mode == FLAGG_TRIMMED_MEAN) ? CS_TRIMMED_ANY : (e->n == n ? CS_MEDIAN_EXACT : CS_MEDIAN_ANY);
+        const bool exact = (e->n == n);
+        const int variant = (mode == FLAGG_TRIMMED_MEAN) ? (exact ? CS_TRIMMED_EXACT : CS_TRIMMED_ANY)
+                                                         : (exact ? CS_MEDIAN_EXACT : CS_MEDIAN_ANY);
         return e->fn(v->dev, variant, k, out, units, sms, st);
     }
     const size_t smem = sizeof(float*) * size_t(n) + sizeof(int) * 16 * RX_THREADS;

@@ -82,6 +82,16 @@ def verify(n, ops, outs, trials=200):
             assert w[o] == s[o], (n, o)
 
 
+def mix_for(n):
+    """(num, den): share of full compare-exchanges whose max goes to the FMA pipe.  Tuned on B200
+    (tools/k1_tune): large networks are ALU/issue co-bound and want ~3/5; small ones are HBM-bound."""
+    env = os.environ.get("FLAGG_MIX")
+    if env:
+        a, b = env.split("/")
+        return int(a), int(b)
+    return (2, 3) if n >= 48 else (5, 8)
+
+
 def emit(n):
     full = oddeven_merge_sort(n)
     full_ops = [(a, b, True, True) for a, b in full]
@@ -91,11 +101,15 @@ def emit(n):
     verify(n, med, [r])
 
     def body(ops):
+        # A fraction MIX of the full compare-exchanges computes its upper output on the FMA pipe
+        # (CE1, two IMADs) instead of the ALU pipe (CE0, FMNMX); spread evenly (Bresenham).
         out = []
         nfull = 0
+        num, den = mix_for(n)
         for a, b, lo, hi in ops:
             if lo and hi:
-                out.append(f"CE({a},{b},{nfull})")
+                on_fma = ((nfull + 1) * num) // den - (nfull * num) // den
+                out.append(f"CE{on_fma}({a},{b})")
                 nfull += 1
             else:
                 out.append(f"{'CE_LO' if lo else 'CE_HI'}({a},{b})")
@@ -104,10 +118,16 @@ def emit(n):
             lines.append("    " + " ".join(out[i:i + 8]))
         return "\n".join(lines)
 
+    # runtime n in (prev, N] (prev = next smaller generated size): rank (n-1)//2 lies in [prev//2, (N-1)//2]
+    prev = max([m for m in SIZES if m < n], default=1)
+    rmin = prev // 2
+    med_any = prune_to_outputs(full, list(range(rmin, r + 1)))
+    verify(n, med_any, range(rmin, r + 1))
     nops_med = sum(int(lo) + int(hi) for _, _, lo, hi in med)
     txt = f"// N={n}: sort {len(full)} CE ({2 * len(full)} min/max); median(rank {r}) {len(med)} CE ({nops_med} min/max)\n"
     txt += f"template <> __device__ __forceinline__ void Net<{n}>::sort(float (&v)[{n}], int one, int mone) {{\n{body(full_ops)}\n}}\n"
     txt += f"template <> __device__ __forceinline__ float Net<{n}>::median(float (&v)[{n}], int one, int mone) {{\n{body(med)}\n    return v[{r}];\n}}\n"
+    txt += f"template <> __device__ __forceinline__ void Net<{n}>::median_any(float (&v)[{n}], int one, int mone) {{\n{body(med_any)}\n}}\n"
     return txt, len(full), len(med), nops_med
 
 
@@ -143,6 +163,9 @@ def main():
         fh.write("// GENERATED by gen_networks.py -- do not edit.\n#pragma once\n")
         fh.write("#define FLAGG_NET_SIZES(X) " + " ".join(f"X({n})" for n in SIZES) + "\n")
         fh.write(f"#define FLAGG_NET_MAX {max(SIZES)}\n")
+        # next smaller generated size: a network of size N serves n in (net_prev(N), N]
+        chain = " ".join(f"n == {n} ? {max([m for m in SIZES if m < n], default=1)} :" for n in SIZES)
+        fh.write(f"__host__ __device__ constexpr int net_prev(int n) {{ return {chain} 1; }}\n")
     if "-v" in sys.argv:
         for n, nf, nm, nom in sorted(stats):
             print(f"N={n:4d} sort={nf:5d} CE  median={nm:5d} CE / {nom:5d} min-max ops")
