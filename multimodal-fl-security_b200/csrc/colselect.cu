@@ -7,6 +7,9 @@
 // atomics).  The column is re-read from L2/HBM on every pass -- 8 passes for a median,
 // 17 for a trimmed mean -- so this path is a correctness fallback, not a roofline
 // kernel (DESIGN.md says so); every load is still a full coalesced 128-byte line.
+#include <cstdlib>
+#include <cstring>
+
 #include "colselect_net.cuh"
 #include "network_sizes.h"
 
@@ -89,7 +92,7 @@ colselect_radix_kernel(ViewDev v, int mode, int k, float* __restrict__ out, int6
             const int kk = int(uk ^ 0x80000000u);
             bool has_nan = false;
             for (int i = 0; i < n; ++i) { const float x = sptr[i][c]; has_nan |= (x != x); }
-            if (has_nan || kk == 0 || kk == -1) res = median_slow(sptr, n, c, res);
+            if (has_nan || kk == 0 || kk == -1) res = median_slow(sptr, 1, n, c, res);
         } else {
             const unsigned uL = radix_select(sptr, n, c, k, hist);
             const unsigned uH = radix_select(sptr, n, c, n - k - 1, hist);
@@ -148,7 +151,16 @@ extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float*
         const bool exact = (e->n == n);
         const int variant = (mode == FLAGG_TRIMMED_MEAN) ? (exact ? CS_TRIMMED_EXACT : CS_TRIMMED_ANY)
                                                          : (exact ? CS_MEDIAN_EXACT : CS_MEDIAN_ANY);
-        return e->fn(v->dev, variant, k, out, units, sms, st);
+        // TMA-staged feed for the exact sizes on 16-byte aligned tensors; FLAGG_K1_IMPL=ldg|bulk overrides (tests, tuning)
+        const char* impl = getenv("FLAGG_K1_IMPL");
+        const bool want_bulk = impl ? !strcmp(impl, "bulk") : true;
+        if (impl && !strcmp(impl, "bulk") && !(exact && v->align_bytes >= 16)) {
+            set_error("flagg_colwise_select: FLAGG_K1_IMPL=bulk needs n in the generated sizes and 16-byte aligned tensors");
+            return FLAGG_EUNSUPPORTED;
+        }
+        const bool force_bulk = impl && !strcmp(impl, "bulk");
+        const int flag = (want_bulk && exact && v->align_bytes >= 16 && (v->dense || force_bulk)) ? CS_BULK : 0;
+        return e->fn(v->dev, variant | flag, k, out, units, sms, st);
     }
     const size_t smem = sizeof(float*) * size_t(n) + sizeof(int) * 16 * RX_THREADS;
     FLAGG_REQUIRE(smem <= 200 * 1024, "flagg_colwise_select: n=%d too large", n);

@@ -37,6 +37,9 @@ struct ViewDev {
     const int64_t* unit_start[3];  // [P+1] each: prefix of UNIT_COLS[g]-wide column units per segment
     int n, P;
     int64_t d;
+    // CUtensorMap[P] (64 B each, device memory) when every tensor is one dense [n x len] matrix
+    // with a 16-byte-multiple row pitch -- box {128 columns, n rows}; nullptr otherwise.
+    const void* tmaps;
 };
 
 // Work is indexed in "units": runs of UNIT_COLS[g] columns that never cross a segment
@@ -58,6 +61,7 @@ struct flagg_view {
     void* d_scratch = nullptr;     // weights / row indices for row_combine, partials
     size_t scratch_bytes = 0;
     int align_bytes = 4;           // min alignment over all segment base addresses (4/8/16)
+    bool dense = false;            // dev.tmaps is valid (see ViewDev::tmaps)
     int64_t total_units[flagg::NUM_GRAN] = {0, 0, 0};
     int device = 0;
     int ensure_scratch(size_t bytes);

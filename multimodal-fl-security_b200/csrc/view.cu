@@ -1,5 +1,7 @@
 // flagg_view: the n x P segmented description of the client-update matrix, plus
 // library-level plumbing (error string, device info).
+#include <cuda.h>
+#include <cudaTypedefs.h>
 #include <stdarg.h>
 #include <string.h>
 
@@ -14,6 +16,21 @@ void set_error(const char* fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency).
+static PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    }
+    return fn;
 }
 
 int device_sm_count() {
@@ -88,9 +105,38 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
     cudaError_t e = cudaGetDevice(&v->device);
     if (e != cudaSuccess) { delete v; set_error("cudaGetDevice: %s", cudaGetErrorString(e)); return FLAGG_ECUDA; }
 
+    // Dense detection: rows of every tensor equally spaced (one [n x len] matrix per tensor, e.g. the
+    // rows of a stacked update matrix or flagg_upload_rows' staging matrix) -> 2-D TMA tensor maps.
+    std::vector<CUtensorMap> tmaps;
+    if (n >= 2 && n <= 256 && align == 16) {
+        PFN_cuTensorMapEncodeTiled_v12000 encode = tensor_map_encoder();
+        bool ok = encode != nullptr;
+        tmaps.resize(P);
+        memset(tmaps.data(), 0, sizeof(CUtensorMap) * P);
+        for (int p = 0; p < P && ok; ++p) {
+            if (v->seg_numel[p] == 0) continue;
+            const char* r0 = static_cast<const char*>(v->seg_ptrs[p]);
+            const int64_t pitch = static_cast<const char*>(v->seg_ptrs[size_t(P) + p]) - r0;
+            ok = pitch >= 4 * v->seg_numel[p] && (pitch & 15) == 0 && pitch < (int64_t(1) << 40) &&
+                 v->seg_numel[p] < (int64_t(1) << 31);
+            for (int i = 2; i < n && ok; ++i) ok = static_cast<const char*>(v->seg_ptrs[size_t(i) * P + p]) == r0 + int64_t(i) * pitch;
+            if (!ok) break;
+            const cuuint64_t gdim[2] = {cuuint64_t(v->seg_numel[p]), cuuint64_t(n)};
+            const cuuint64_t gstride[1] = {cuuint64_t(pitch)};
+            const cuuint32_t box[2] = {128u, cuuint32_t(n)};
+            const cuuint32_t estride[2] = {1u, 1u};
+            const CUresult r = encode(&tmaps[p], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<char*>(r0), gdim, gstride, box,
+                                      estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            ok = (r == CUDA_SUCCESS);
+        }
+        v->dense = ok;
+    }
+
     const size_t b_ptrs = sizeof(void*) * size_t(n) * P;
     const size_t b_pref = sizeof(int64_t) * (P + 1);
-    const size_t total = b_ptrs + (1 + NUM_GRAN) * b_pref;
+    const size_t b_tabs = (b_ptrs + (1 + NUM_GRAN) * b_pref + 63) & ~size_t(63);   // tensor maps need 64-byte alignment
+    const size_t total = b_tabs + (v->dense ? sizeof(CUtensorMap) * P : 0);
     e = cudaMalloc(&v->d_tables, total);
     if (e != cudaSuccess) { delete v; set_error("cudaMalloc(view tables, %zu B): %s", total, cudaGetErrorString(e)); return FLAGG_ECUDA; }
     char* base = static_cast<char*>(v->d_tables);
@@ -101,6 +147,8 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
     if (e == cudaSuccess) e = cudaMemcpyAsync(base + b_ptrs, v->seg_start.data(), b_pref, cudaMemcpyHostToDevice, st);
     for (int g = 0; g < NUM_GRAN && e == cudaSuccess; ++g)
         e = cudaMemcpyAsync(base + b_ptrs + (1 + g) * b_pref, v->unit_start[g].data(), b_pref, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && v->dense)
+        e = cudaMemcpyAsync(base + b_tabs, tmaps.data(), sizeof(CUtensorMap) * P, cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) {
         set_error("flagg_view_create: table upload failed: %s", cudaGetErrorString(e));
         cudaFree(v->d_tables);
@@ -111,6 +159,7 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
     v->dev.seg_start = reinterpret_cast<const int64_t*>(base + b_ptrs);
     for (int g = 0; g < NUM_GRAN; ++g)
         v->dev.unit_start[g] = reinterpret_cast<const int64_t*>(base + b_ptrs + (1 + g) * b_pref);
+    v->dev.tmaps = v->dense ? base + b_tabs : nullptr;
     v->dev.n = n;
     v->dev.P = P;
     v->dev.d = v->seg_start[P];
