@@ -299,8 +299,8 @@ def run_flagg(args, rank, world, local_rank):
                        "l2_policy": "inputs (10 GB) larger than L2 (126 MB); no flush needed",
                        "clients_x_params_per_s": world * n * d * args.steps / t},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                         "traffic": ncu_traffic("colselect_net_kernel<100,median>"), "peak_source": which,
-                         "algorithmic_bytes_per_launch": alg_bytes, "kernel": "colselect_net_kernel<100, MEDIAN_EXACT>"},
+                         "traffic": ncu_traffic("colselect_bulk_kernel<100,median>"), "peak_source": which,
+                         "algorithmic_bytes_per_launch": alg_bytes, "kernel": "colselect_bulk_kernel<100, MEDIAN_EXACT> (2-D TMA feed; the input is one dense matrix)"},
             "e2e": {"value": e2e, "unit": "GB/s", "h2d_bytes_per_step": 4 * n * d, "d2h_bytes_per_step": 4 * d,
                     "steps": e2e_steps, "api": "src.defenses.MedianDefense.aggregate(pinned host tensors)",
                     "matches_device_result": same, "pinned_h2d_memcpy_GBps": pcie},

@@ -53,6 +53,54 @@ def test_median_every_network_size(n):
     assert np.array_equal(bits(got), bits(oracle64.median_stable(X))), n
 
 
+def dense_lists(X, seg, pitch_pad=4):
+    """Rows as slices of ONE device matrix whose row pitch is a multiple of 16 bytes: the layout
+    flagg_view_create recognises as dense and feeds through 2-D TMA tensor maps (tensors whose
+    column offset is a multiple of 4 floats; otherwise the view is not 16-byte aligned and the
+    LDG kernel runs)."""
+    n, d = X.shape
+    ld = (d + 3) // 4 * 4 + pitch_pad
+    big = torch.full((n, ld), float("nan"), device="cuda")
+    big[:, :d] = torch.from_numpy(X).cuda()
+    offs = np.concatenate([[0], np.cumsum(seg)]).astype(int)
+    return big, [[big[i, offs[p]:offs[p + 1]] for p in range(len(seg))] for i in range(n)]
+
+
+@pytest.mark.parametrize("impl", ["default", "ldg", "bulk"])
+@pytest.mark.parametrize("n", [2, 3, 5, 10, 16, 20, 31, 32, 36, 48, 64, 72, 96, 100, 128])
+def test_median_and_trimmed_dense_tma_path(n, impl, monkeypatch):
+    """K1 fed by TMA (2-D tensor-map boxes on a dense matrix; per-row 1-D bulk copies when forced
+    with FLAGG_K1_IMPL=bulk) against the LDG kernel and the oracle: bit-exact median including
+    +-0 / NaN / Inf columns, ragged tails (tensor lengths not multiples of 128 columns, zero-filled
+    by the TMA unit) and several tensors per client."""
+    from flagg import MEDIAN, TRIMMED_MEAN, engine
+    if impl == "default":
+        monkeypatch.delenv("FLAGG_K1_IMPL", raising=False)
+    else:
+        monkeypatch.setenv("FLAGG_K1_IMPL", impl)
+    rng = np.random.RandomState(4000 + n)
+    seg = [256, 4, 1000, 132, 120]                       # every offset a multiple of 4 floats
+    d = sum(seg)
+    X = rows_model(rng, n, d, byz=n // 5)
+    X[:, :150] = rng.choice(EDGE, size=(n, 150))
+    X[:, 150:182] = rng.choice(np.array([0.0, -0.0], dtype=np.float32), size=(n, 32))
+    Xi = X.view(np.uint32)
+    for j in range(182, 200):
+        Xi[rng.randint(n), j] = rng.choice([0x7FC00000, 0xFFC00001, 0x7F800123])
+    big, lists = dense_lists(X, seg)
+    u = engine.Updates(lists)
+    got = engine.colwise_select(u, MEDIAN).cpu().numpy()
+    assert np.array_equal(bits(got), bits(oracle64.median_stable(X))), (n, impl)
+    k = max(1, n // 10)
+    if n - 2 * k >= 1:
+        Xt = X.copy()
+        Xt[:, :200] = rows_model(rng, n, 200)            # finite data for the tolerance comparison
+        big[:, :200] = torch.from_numpy(Xt[:, :200]).cuda()
+        gt = engine.colwise_select(u, TRIMMED_MEAN, k).cpu().numpy()
+        assert_close_scaled(gt, oracle64.trimmed_mean64(Xt, k), oracle64.trimmed_scale(Xt, k), tol=2e-6, what=f"n={n} k={k} {impl}")
+    u.close()
+
+
 @pytest.mark.parametrize("n", [129, 130, 200, 257, 1000])
 def test_median_radix_fallback(n):
     from flagg import MEDIAN
