@@ -27,6 +27,8 @@
 // drains in fp32 (round to nearest) for at most FOLD*KC = 8192 columns, and everything
 // above that is FP64.  D^2 and sqrt are formed in FP64 by K5 (gram.cu).
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 
@@ -235,6 +237,61 @@ __device__ __forceinline__ void split_store(uint32_t hi_addr, uint32_t lo_addr, 
         : "memory");
 }
 
+// Epilogue role (warps 0-3), shared by the SS and TS kernels: every KC columns drain the TMEM
+// accumulator D[buf] into the second-level fp32 accumulator ACC (also TMEM), every FOLD drains
+// fold ACC into the CTA's FP64 partial tile (column-major [128 col][128 row]) in global memory.
+__device__ __forceinline__ void epilogue_role(uint32_t tmem_base, double* __restrict__ part, int ndrain, int warp, int lane,
+                                              uint32_t tfull0, uint32_t tempty0) {
+    const int row = warp * 32 + lane;
+    const uint32_t lane_base = tmem_base + (uint32_t(warp * 32) << 16);
+    double* my = part + (size_t(blockIdx.y) * gridDim.x + blockIdx.x) * (TILE * TILE) + row;
+    bool folded = false;
+    int in_fold = 0;
+    for (int dr = 0; dr < ndrain; ++dr) {
+        const int buf = dr & 1;
+        mbar_wait(tfull0 + 8u * buf, uint32_t((dr >> 1) & 1));
+        tc_fence_after();
+#pragma unroll 1
+        for (int g = 0; g < TILE / EG; ++g) {
+            float x[EG];
+            tmem_ld16(lane_base + uint32_t(buf * TILE + g * EG), x);
+            if (in_fold > 0) {
+                float a[EG];
+                tmem_ld16(lane_base + uint32_t(2 * TILE + g * EG), a);
+                tmem_wait_ld();
+#pragma unroll
+                for (int e = 0; e < EG; ++e) x[e] = __fadd_rn(x[e], a[e]);
+            } else {
+                tmem_wait_ld();
+            }
+            tmem_st16(lane_base + uint32_t(2 * TILE + g * EG), x);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty0 + 8u * buf);
+        ++in_fold;
+        if (in_fold == FOLD || dr == ndrain - 1) {
+#pragma unroll 1
+            for (int g = 0; g < TILE / EG; ++g) {
+                float a[EG];
+                tmem_ld16(lane_base + uint32_t(2 * TILE + g * EG), a);
+                tmem_wait_ld();
+#pragma unroll
+                for (int e = 0; e < EG; ++e) {
+                    double* q = my + size_t(g * EG + e) * TILE;
+                    *q = folded ? *q + double(a[e]) : double(a[e]);
+                }
+            }
+            folded = true;
+            in_fold = 0;
+        }
+    }
+    if (ndrain == 0) {
+        for (int c = 0; c < TILE; ++c) my[size_t(c) * TILE] = 0.0;
+    }
+}
+
 // grid = (tiles, splits).  part: per-CTA FP64 partial tile, COLUMN-major [128 col][128 row].
 __global__ void __launch_bounds__(THREADS, 1)
 gram_tc_kernel(ViewDev v, const float* __restrict__ center, int nb, int64_t total_units, int64_t units_per_split,
@@ -377,54 +434,7 @@ gram_tc_kernel(ViewDev v, const float* __restrict__ center, int nb, int64_t tota
         }
     } else {
         // ================================ epilogue ================================
-        const int row = warp * 32 + lane;
-        const uint32_t lane_base = tmem_base + (uint32_t(warp * 32) << 16);
-        double* my = part + (size_t(blockIdx.y) * gridDim.x + blockIdx.x) * (TILE * TILE) + row;
-        bool folded = false;
-        int in_fold = 0;
-        for (int dr = 0; dr < ndrain; ++dr) {
-            const int buf = dr & 1;
-            mbar_wait(TFULL(buf), uint32_t((dr >> 1) & 1));
-            tc_fence_after();
-#pragma unroll 1
-            for (int g = 0; g < TILE / EG; ++g) {
-                float x[EG];
-                tmem_ld16(lane_base + uint32_t(buf * TILE + g * EG), x);
-                if (in_fold > 0) {
-                    float a[EG];
-                    tmem_ld16(lane_base + uint32_t(2 * TILE + g * EG), a);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int e = 0; e < EG; ++e) x[e] = __fadd_rn(x[e], a[e]);
-                } else {
-                    tmem_wait_ld();
-                }
-                tmem_st16(lane_base + uint32_t(2 * TILE + g * EG), x);
-            }
-            tmem_wait_st();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(TEMPTY(buf));
-            ++in_fold;
-            if (in_fold == FOLD || dr == ndrain - 1) {
-#pragma unroll 1
-                for (int g = 0; g < TILE / EG; ++g) {
-                    float a[EG];
-                    tmem_ld16(lane_base + uint32_t(2 * TILE + g * EG), a);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int e = 0; e < EG; ++e) {
-                        double* q = my + size_t(g * EG + e) * TILE;
-                        *q = folded ? *q + double(a[e]) : double(a[e]);
-                    }
-                }
-                folded = true;
-                in_fold = 0;
-            }
-        }
-        if (ndrain == 0) {
-            for (int c = 0; c < TILE; ++c) my[size_t(c) * TILE] = 0.0;
-        }
+        epilogue_role(tmem_base, part, ndrain, warp, lane, TFULL(0), TEMPTY(0));
     }
     tc_fence_before();
     __syncthreads();
@@ -433,6 +443,8 @@ gram_tc_kernel(ViewDev v, const float* __restrict__ center, int nb, int64_t tota
         tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
+
+#include "gram_ts.cuh"
 
 // Sum the split partials in split order and scatter the tile (and its mirror) into G.
 __global__ void gram_tc_reduce_kernel(const double* __restrict__ part, int tiles, int splits, int nb, int n,
@@ -476,13 +488,20 @@ int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G
     int rc = v->ensure_scratch(need);
     if (rc != FLAGG_OK) return rc;
     double* part = static_cast<double*>(v->d_scratch);
+    // Default: both operands in shared memory.  FLAGG_GRAM_IMPL=ts feeds A from tensor memory
+    // (gram_ts.cuh): correct, but no faster -- both kernels sit on the L2->SM operand feed
+    // (profiles/r01_k4_load_ubench.txt), not on shared-memory bandwidth.
+    const char* impl = getenv("FLAGG_GRAM_IMPL");
+    const bool ss = !(impl && !strcmp(impl, "ts"));
     static bool attr_set = false;
     if (!attr_set) {
         FLAGG_CUDA(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        FLAGG_CUDA(cudaFuncSetAttribute(gram_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_BYTES));
         attr_set = true;
     }
     dim3 grid(tiles, unsigned(splits));
-    gram_tc_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
+    if (ss) gram_tc_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
+    else gram_ts_kernel<<<grid, THREADS, TS_SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
     FLAGG_CUDA(cudaGetLastError());
     gram_tc_reduce_kernel<<<dim3(tiles, 16), 256, 0, st>>>(part, tiles, int(splits), nb, n, accumulate, G);
     FLAGG_CUDA(cudaGetLastError());

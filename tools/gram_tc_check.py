@@ -66,17 +66,20 @@ def tf32_peak():
 if __name__ == "__main__":
     bad = 0
     if "--only-time" in sys.argv:
-        timing(1000, 3_125_000, "tc", reps=2)
+        timing(1000, 3_125_000, sys.argv[-1] if sys.argv[-1] in ("tc", "ss", "ts") else "tc", reps=2)
         sys.exit(0)
     if "--peak" in sys.argv:
         tf32_peak()
     for n, segs in [(64, [4096]), (128, [32]), (128, [256 * 40]), (65, [3000]), (130, [2049 - 1, 1]), (200, [777 + 3, 64, 5000]),
                     (300, [100000]), (1000, [70000, 36, 30000])]:
-        for impl in ("tc", "ffma"):
+        for impl in ("tc", "ts", "ffma"):
             eg, ed = check(n, segs, impl)
             bad += (ed > 1e-5) or not np.isfinite(ed)
     if "--time" in sys.argv:
         timing(1000, 3_125_000, "tc")
+        timing(1000, 3_125_000, "ts")
+        timing(500, 3_125_000, "tc")
+        timing(128, 3_125_000, "tc")
         timing(1000, 3_125_000, "ffma", reps=1)
         timing(100, 25_000_000 // 8, "tc")
         timing(500, 1_461_188, "tc")
