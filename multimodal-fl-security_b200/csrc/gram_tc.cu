@@ -445,6 +445,7 @@ gram_tc_kernel(ViewDev v, const float* __restrict__ center, int nb, int64_t tota
 }
 
 #include "gram_ts.cuh"
+#include "gram_ts2.cuh"
 
 // Sum the split partials in split order and scatter the tile (and its mirror) into G.
 __global__ void gram_tc_reduce_kernel(const double* __restrict__ part, int tiles, int splits, int nb, int n,
@@ -472,14 +473,44 @@ __global__ void gram_tc_reduce_kernel(const double* __restrict__ part, int tiles
 }  // namespace tc
 
 // Host launch; called from flagg_gram (gram.cu).  Requires 16-byte aligned segment bases.
+// Kernel choice (FLAGG_GRAM_IMPL=ss|ts|ts2 overrides): n > 256 -> CTA-pair 256x256 tiles
+// (gram_ts2.cuh); otherwise 128x128 tiles with both operands in shared memory.
 int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st) {
     using namespace tc;
     const int n = v->dev.n;
-    const int nb = (n + TILE - 1) / TILE;
-    const int tiles = nb * (nb + 1) / 2;
     const int64_t units = v->total_units[GRAN_128];
     FLAGG_REQUIRE(units < (int64_t(1) << 31), "flagg_gram: too many columns for the tensor-core path");
     const int sms = device_sm_count();
+    const char* impl = getenv("FLAGG_GRAM_IMPL");
+    const bool want_ss = impl && !strcmp(impl, "ss"), want_ts = impl && !strcmp(impl, "ts"), want_ts2 = impl && !strcmp(impl, "ts2");
+    const bool pair = want_ts2 || (!want_ss && !want_ts && n > T2_ROWS);
+    static bool attr_set = false;
+    if (!attr_set) {
+        FLAGG_CUDA(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        FLAGG_CUDA(cudaFuncSetAttribute(gram_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_BYTES));
+        FLAGG_CUDA(cudaFuncSetAttribute(gram_ts2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
+        attr_set = true;
+    }
+    if (pair) {
+        const int nb2 = (n + T2_ROWS - 1) / T2_ROWS;
+        const int tiles2 = nb2 * (nb2 + 1) / 2;
+        int64_t splits = std::max<int64_t>(1, sms / (2 * tiles2));
+        splits = std::min<int64_t>(splits, units);
+        const int64_t upb = (units + splits - 1) / splits;
+        splits = (units + upb - 1) / upb;
+        const size_t need = sizeof(double) * size_t(splits) * tiles2 * 2 * (2 * TILE * TILE);
+        int rc = v->ensure_scratch(need);
+        if (rc != FLAGG_OK) return rc;
+        double* part = static_cast<double*>(v->d_scratch);
+        dim3 grid(2 * tiles2, unsigned(splits));
+        gram_ts2_kernel<<<grid, THREADS, T2_SMEM_BYTES, st>>>(v->dev, center, nb2, units, upb, part);
+        FLAGG_CUDA(cudaGetLastError());
+        gram_ts2_reduce_kernel<<<dim3(2 * tiles2, 16), 256, 0, st>>>(part, tiles2, int(splits), nb2, n, accumulate, G);
+        FLAGG_CUDA(cudaGetLastError());
+        return FLAGG_OK;
+    }
+    const int nb = (n + TILE - 1) / TILE;
+    const int tiles = nb * (nb + 1) / 2;
     int64_t splits = std::max<int64_t>(1, sms / tiles);
     splits = std::min<int64_t>(splits, units);
     const int64_t upb = (units + splits - 1) / splits;
@@ -488,20 +519,9 @@ int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G
     int rc = v->ensure_scratch(need);
     if (rc != FLAGG_OK) return rc;
     double* part = static_cast<double*>(v->d_scratch);
-    // Default: both operands in shared memory.  FLAGG_GRAM_IMPL=ts feeds A from tensor memory
-    // (gram_ts.cuh): correct, but no faster -- both kernels sit on the L2->SM operand feed
-    // (profiles/r01_k4_load_ubench.txt), not on shared-memory bandwidth.
-    const char* impl = getenv("FLAGG_GRAM_IMPL");
-    const bool ss = !(impl && !strcmp(impl, "ts"));
-    static bool attr_set = false;
-    if (!attr_set) {
-        FLAGG_CUDA(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        FLAGG_CUDA(cudaFuncSetAttribute(gram_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_BYTES));
-        attr_set = true;
-    }
     dim3 grid(tiles, unsigned(splits));
-    if (ss) gram_tc_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
-    else gram_ts_kernel<<<grid, THREADS, TS_SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
+    if (want_ts) gram_ts_kernel<<<grid, THREADS, TS_SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
+    else gram_tc_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
     FLAGG_CUDA(cudaGetLastError());
     gram_tc_reduce_kernel<<<dim3(tiles, 16), 256, 0, st>>>(part, tiles, int(splits), nb, n, accumulate, G);
     FLAGG_CUDA(cudaGetLastError());

@@ -1,0 +1,410 @@
+// K4, CTA-pair variant: 256 x 256 output tiles on two SMs (tcgen05 cta_group::2), A operand from
+// tensor memory, B from shared memory.  Included by gram_tc.cu inside namespace flagg::tc after
+// gram_ts.cuh (shares ts_load, the PTX wrappers, KbIter).  Replaces krum.py:92-97 for n > 256.
+//
+// Why pairs.  The 128 x 128 kernels are bound by the L2 -> SM operand feed: every CTA pulls 32 KB
+// per 32-column k-block for 12 MMAs, and the pattern tops out at ~4.9 TB/s over the chip
+// (profiles/r01_k4_load_ubench.txt: 23.3 ms for the C4 shard with no other work).  A CTA pair
+// computing 256 x 256 pulls the same 32 KB per CTA per k-block for 24 MMAs: half the bytes per flop.
+//
+// Geometry of pair tile (BI, BJ), CTA rank r in {0, 1}:
+//   A rows  BI*256 + 128 r + [0,128)  -> this CTA's TMEM lanes (UMMA M = 256 spans both CTAs)
+//   B rows  BJ*256 + 128 r + [0,128)  -> this CTA's shared memory; local row b belongs to N-half
+//           hf = b / 64 and is row b % 64 of that half's operand tile.  On diagonal tiles
+//           (BI == BJ) the B rows ARE the A rows, so one set of loads feeds both.
+//   Each k-step issues, per N-half, three MMAs (M = 256, N = 128: 64 rows of B from each CTA)
+//   hi*hi, hi*lo, lo*hi into that half's accumulator region.  Output column c of half hf is
+//   B row 128 (c / 64) + 64 hf + (c % 64) of the block (gram_ts2_reduce_kernel undoes this).
+//
+// TMEM (512 columns): three 128-column accumulator regions + 128 columns of A stages.  The two
+// N-halves accumulate into two regions while the third is drained; their KC-column chunks are
+// staggered by KC/2 so drain events alternate (event e: half (e+1)&1, region e%3; the chunk that
+// starts after event e takes region (e+2)%3).  The second accumulation level (fp32, at most
+// FOLD drains = 8192 columns) lives in SHARED memory here (128 KB), the third is FP64 in global.
+//
+// Synchronisation: FULL[st] (16 producer-warp arrivals, both CTAs) and TEMPTY[region] (8 epilogue-
+// warp arrivals) live in the leader CTA (rank 0) whose MMA warp issues every MMA; EMPTY[st] and
+// TFULL[region] are per CTA and signalled by multicast tcgen05.commit.
+#pragma once
+
+constexpr int T2_ROWS = 256;                          // pair-tile edge
+constexpr int T2_BTILE_BYTES = 64 * BK * 4;           // one B operand tile: 64 rows x 32 K = 8 KB
+constexpr int T2_SLOT_BYTES = 4 * T2_BTILE_BYTES;     // [half][hi, lo]
+constexpr int T2_SLOTS = 2;                           // k-blocks of B in flight
+constexpr int T2_NSTG = 4;                            // stages of 16 K positions (2 per k-block)
+constexpr int T2_ACC_BYTES = 2 * TILE * TILE * 4;     // second-level accumulator [half][col][row] fp32
+constexpr int T2_TMEM_A0 = 3 * TILE;
+constexpr int T2_BAR_OFF = T2_SLOTS * T2_SLOT_BYTES + T2_ACC_BYTES;
+constexpr int T2_SMEM_BYTES = T2_BAR_OFF + 1024 + 256;
+constexpr int T2_CHUNK = KC_BLOCKS;                   // k-blocks per first-level chunk (KC = 256 columns)
+constexpr uint32_t IDESC2 = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(128 >> 3) << 17) | (uint32_t(256 >> 4) << 24);
+static_assert(T2_SMEM_BYTES <= 232448, "shared memory budget");
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `local_addr` in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "LAB_WAITC: mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra LAB_DONEC;\n\tbra LAB_WAITC;\n\tLAB_DONEC:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma2_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "r"(a_tmem), "l"(b_desc), "r"(IDESC2), "r"(accumulate)
+        : "memory");
+}
+// arrive (count 1) on the barrier at this shared::cta offset in BOTH CTAs of the pair once all
+// prior MMAs of this thread have completed
+__device__ __forceinline__ void umma2_commit_both(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+                 "h"(uint16_t(3))
+                 : "memory");
+}
+
+__device__ __forceinline__ uint64_t pack2(float a, float b) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ uint64_t sub2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
+gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t total_units, int64_t units_per_split,
+                double* __restrict__ part) {
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    unsigned char* smem = smem_raw + (sbase - smem_u32(smem_raw));
+    float* acc = reinterpret_cast<float*>(smem + T2_SLOTS * T2_SLOT_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + T2_BAR_OFF);
+    // bars: [0,4) FULL (leader's used), [4,8) EMPTY, [8,11) TFULL, [11,14) TEMPTY (leader's used)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+    int* nkb_slot = reinterpret_cast<int*>(bars + 15);
+    const uint32_t bar0 = sbase + T2_BAR_OFF;
+    auto FULL = [&](int s) { return bar0 + 8u * s; };
+    auto EMPTY = [&](int s) { return bar0 + 8u * (4 + s); };
+    auto TFULL = [&](int r) { return bar0 + 8u * (8 + r); };
+    auto TEMPTY = [&](int r) { return bar0 + 8u * (11 + r); };
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = cluster_ctarank();
+    int t = int(blockIdx.x >> 1), BI = 0;
+    while (t >= nb2 - BI) { t -= nb2 - BI; ++BI; }
+    const int BJ = BI + t;
+    const bool diag = (BI == BJ);
+    const int64_t u0 = int64_t(blockIdx.y) * units_per_split;
+    const int64_t u1 = min(total_units, u0 + units_per_split);
+
+    if (tid == 0) {
+        for (int s = 0; s < T2_NSTG; ++s) { mbar_init(FULL(s), 2 * PROD_WARPS); mbar_init(EMPTY(s), 1); }
+        for (int r = 0; r < 3; ++r) { mbar_init(TFULL(r), 1); mbar_init(TEMPTY(r), 2 * EPI_WARPS); }
+        fence_barrier_init();
+        *nkb_slot = int(count_kblocks(v, u0, u1));
+    }
+    if (warp == MMA_WARP) tmem_alloc2(smem_u32(tmem_slot), TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();          // both CTAs' barriers are initialised before any remote arrive
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int nkb = *nkb_slot;
+    // drain events: one every CHUNK/2 k-blocks strictly inside the range, two at the end
+    const int n_ev = nkb > 0 ? (nkb - 1) / (T2_CHUNK / 2) + 2 : 0;
+
+    if (warp >= EPI_WARPS && warp < MMA_WARP) {
+        // ================================ producers ================================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(TS_PROD_REGS));
+        const int qd = warp & 3, h16 = (warp - EPI_WARPS) >> 2;
+        const int lane0 = 32 * qd + 16 * h16;           // first TMEM lane = first local row of this warp
+        const int r8 = lane >> 2, q = lane & 3;
+        const int rloc = lane0 + r8;                    // local rows rloc, rloc + 8
+        const int hf = qd >> 1, brow = rloc & 63;       // N-half and row inside that half's B tile
+        // B byte offset of K position 2q of row brow (see gram_ts.cuh); odd rows of an 8-row group
+        // take the OTHER k-step of the stage (^ 64 bytes) so a half-warp's 8-byte stores hit 16
+        // distinct bank pairs
+        const uint32_t boff = uint32_t(hf) * (2u * T2_BTILE_BYTES) + uint32_t(brow >> 3) * 1024u + uint32_t(brow & 7) * 128u +
+                              ((uint32_t((q >> 1) ^ (brow & 7)) << 4) + uint32_t(q & 1) * 8u);
+        const bool odd = (r8 & 1) != 0;
+        bool okA[2], okB[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            okA[h] = (BI * T2_ROWS + int(rank) * TILE + rloc + 8 * h) < v.n;
+            okB[h] = (BJ * T2_ROWS + int(rank) * TILE + rloc + 8 * h) < v.n;
+        }
+        // padding rows of B stay zero for the whole kernel (their stores are predicated off)
+        for (int s = 0; s < T2_SLOTS; ++s)
+            for (int o = 0; o < 2; ++o)
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int g = 0; g < 4; ++g)
+                        *reinterpret_cast<uint2*>(smem + s * T2_SLOT_BYTES + o * T2_BTILE_BYTES + ((boff + h * 1024u) ^ (uint32_t(g) << 5))) =
+                            make_uint2(0u, 0u);
+        TsRows rows;
+        int cur_p = -1;
+        auto refresh_rows = [&](int p) {
+            uintptr_t bits = 0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int ra = min(BI * T2_ROWS + int(rank) * TILE + rloc + 8 * h, v.n - 1);
+                const int rb = min(BJ * T2_ROWS + int(rank) * TILE + rloc + 8 * h, v.n - 1);
+                rows.a[h] = v.seg_ptrs[size_t(ra) * v.P + p];
+                rows.b[h] = v.seg_ptrs[size_t(rb) * v.P + p];
+                bits |= reinterpret_cast<uintptr_t>(rows.a[h]) | reinterpret_cast<uintptr_t>(rows.b[h]);
+            }
+            rows.cbase = center ? center + v.seg_start[p] : nullptr;
+            rows.v8 = (bits & 31) == 0;
+            cur_p = p;
+        };
+        KbIter it;
+        it.init(v, u0, u1);
+        TsRegs r0, r1;
+        auto fetch = [&](TsRegs& r) {
+            if (it.valid()) {
+                if (it.p != cur_p) refresh_rows(it.p);
+                ts_load(it, rows, diag, q, r);
+                it.next(v);
+            }
+        };
+        fetch(r0);
+        fetch(r1);
+        int stage = 0;
+        uint32_t phase = 1;
+        const uint32_t a_lane = tmem_base + (uint32_t(lane0) << 16) + T2_TMEM_A0;
+        const uint32_t full_leader = map_to_cta(FULL(0), 0);
+        constexpr uint64_t HI2 = 0xffffe000ffffe000ull;
+        auto emit = [&](const TsRegs& r) {
+#pragma unroll
+            for (int sub = 0; sub < 2; ++sub) {
+                // this stage's two k-steps are value pairs g = sub and g = sub + 2 of the thread's 8 columns
+                uint64_t ah[2][2], al[2][2], bh[2][2], bl[2][2];   // [row h][k-step j]
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const int g = sub + 2 * j;
+                    const uint64_t c2 = pack2(r.c[2 * g], r.c[2 * g + 1]);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const uint64_t ta = okA[h] ? sub2(pack2(r.a[h][2 * g], r.a[h][2 * g + 1]), c2) : 0ull;
+                        ah[h][j] = ta & HI2;
+                        al[h][j] = sub2(ta, ah[h][j]);
+                        if (diag) {
+                            bh[h][j] = ah[h][j];
+                            bl[h][j] = al[h][j];
+                        } else {
+                            const uint64_t tb = sub2(pack2(r.b[h][2 * g], r.b[h][2 * g + 1]), c2);
+                            bh[h][j] = tb & HI2;
+                            bl[h][j] = sub2(tb, bh[h][j]);
+                        }
+                    }
+                }
+                mbar_wait(EMPTY(stage), phase);
+                tc_fence_after();
+                // A -> TMEM: fragment register 4 j + 2 h + e = (row h, k-step j, element e)
+                uint32_t fh[8], fl[8];
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        fh[4 * j + 2 * h] = uint32_t(ah[h][j]);
+                        fh[4 * j + 2 * h + 1] = uint32_t(ah[h][j] >> 32);
+                        fl[4 * j + 2 * h] = uint32_t(al[h][j]);
+                        fl[4 * j + 2 * h + 1] = uint32_t(al[h][j] >> 32);
+                    }
+                tmem_st_16x256b_x2(a_lane + uint32_t(stage * 32), fh);
+                tmem_st_16x256b_x2(a_lane + uint32_t(stage * 32 + 16), fl);
+                // B -> smem: store i writes k-step j = i for even rows, j = 1 - i for odd rows
+                const uint32_t sb = sbase + uint32_t(stage >> 1) * T2_SLOT_BYTES;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        const uint64_t vh = odd ? bh[h][1 - i] : bh[h][i], vl = odd ? bl[h][1 - i] : bl[h][i];
+                        const int ge = sub + 2 * i, go = sub + 2 * (1 - i);
+                        const uint32_t addr = sb + ((boff + h * 1024u) ^ (odd ? uint32_t(go) << 5 : uint32_t(ge) << 5));
+                        if (okB[h]) {
+                            asm volatile("st.shared.b64 [%0], %1;" ::"r"(addr), "l"(vh) : "memory");
+                            asm volatile("st.shared.b64 [%0], %1;" ::"r"(addr + T2_BTILE_BYTES), "l"(vl) : "memory");
+                        }
+                    }
+                }
+                tmem_wait_st();
+                tc_fence_before();
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(full_leader + 8u * stage);
+                if (++stage == T2_NSTG) { stage = 0; phase ^= 1; }
+            }
+        };
+        for (int kb = 0; kb < nkb; kb += 2) {
+            emit(r0);
+            fetch(r0);
+            if (kb + 1 < nkb) {
+                emit(r1);
+                fetch(r1);
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        // ================================ MMA issuer (leader CTA only) ================================
+        if (rank == 0) {
+            int s = 0;
+            uint32_t full_phase = 0;
+            uint32_t tempty_uses = 0;          // bit r: parity of the next wait on TEMPTY[r]
+            int reg[2] = {1, 0};               // accumulator region of half 0 / half 1
+            bool fresh[2] = {true, true};      // next MMA of the half starts a chunk (overwrite)
+            int ev = 0;                        // drain events committed so far
+            for (int kb = 0; kb < nkb; ++kb) {
+#pragma unroll
+                for (int sub = 0; sub < 2; ++sub) {
+                    mbar_wait_cluster(FULL(s), full_phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t slot = sbase + uint32_t(s >> 1) * T2_SLOT_BYTES;
+                        const uint32_t a_hi = tmem_base + T2_TMEM_A0 + uint32_t(s * 32), a_lo = a_hi + 16;
+#pragma unroll
+                        for (int j = 0; j < 2; ++j) {
+                            const uint32_t ko = uint32_t(sub + 2 * j) * 32u;   // k-step g = sub + 2j: bytes inside the 128-byte row
+#pragma unroll
+                            for (int hf = 0; hf < 2; ++hf) {
+                                const uint32_t d = tmem_base + uint32_t(reg[hf] * TILE);
+                                const uint32_t b_hi = slot + uint32_t(hf) * (2u * T2_BTILE_BYTES) + ko, b_lo = b_hi + T2_BTILE_BYTES;
+                                umma2_tf32_ts(d, a_hi + 8 * j, make_desc(b_hi), fresh[hf] ? 0u : 1u);
+                                umma2_tf32_ts(d, a_hi + 8 * j, make_desc(b_lo), 1u);
+                                umma2_tf32_ts(d, a_lo + 8 * j, make_desc(b_hi), 1u);
+                                fresh[hf] = false;
+                            }
+                        }
+                        umma2_commit_both(EMPTY(s));
+                    }
+                    __syncwarp();
+                    if (++s == T2_NSTG) { s = 0; full_phase ^= 1; }
+                }
+                // chunk boundaries after k-block kb: half 1 at 4, 12, 20, ...; half 0 at 8, 16, ...; both at the end
+                const int done = kb + 1;
+                int nclose = 0;
+                if (done == nkb) nclose = 2;
+                else if (done % (T2_CHUNK / 2) == 0) nclose = 1;
+                for (int c = 0; c < nclose; ++c) {
+                    const int hf = (ev + 1) & 1, r = ev % 3;
+                    if (lane == 0) umma2_commit_both(TFULL(r));
+                    __syncwarp();
+                    if (done < nkb) {
+                        // the half continues in region (ev + 2) % 3, which event ev - 1 drained
+                        const int nr = (ev + 2) % 3;
+                        if (ev >= 1) {
+                            mbar_wait_cluster(TEMPTY(nr), (tempty_uses >> nr) & 1u);
+                            tempty_uses ^= 1u << nr;
+                            tc_fence_after();
+                        }
+                        if (hf == 0) { reg[0] = nr; fresh[0] = true; } else { reg[1] = nr; fresh[1] = true; }
+                    }
+                    ++ev;
+                }
+            }
+        }
+    } else {
+        // ================================ epilogue ================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TS_EPI_REGS));
+        const int row = warp * 32 + lane;
+        const uint32_t lane_base = tmem_base + (uint32_t(warp * 32) << 16);
+        double* my = part + ((size_t(blockIdx.y) * (gridDim.x >> 1) + (blockIdx.x >> 1)) * 2 + rank) * (2 * TILE * TILE) + row;
+        const uint32_t tempty_leader = map_to_cta(TEMPTY(0), 0);
+        int cnt[2] = {0, 0};
+        bool folded[2] = {false, false};
+        for (int e = 0; e < n_ev; ++e) {
+            const int r = e % 3, hf = (e + 1) & 1;
+            mbar_wait(TFULL(r), uint32_t((e / 3) & 1));
+            tc_fence_after();
+            float* a = acc + hf * (TILE * TILE) + row;
+            const bool add = cnt[hf] > 0;
+#pragma unroll 1
+            for (int g = 0; g < TILE / EG; ++g) {
+                float x[EG];
+                tmem_ld16(lane_base + uint32_t(r * TILE + g * EG), x);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < EG; ++i) {
+                    float* p = a + (g * EG + i) * TILE;
+                    *p = add ? __fadd_rn(*p, x[i]) : x[i];
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(tempty_leader + 8u * r);
+            ++cnt[hf];
+            if (cnt[hf] == FOLD || e >= n_ev - 2) {
+                double* o = my + size_t(hf) * (TILE * TILE);
+#pragma unroll 4
+                for (int c = 0; c < TILE; ++c) {
+                    const double x = double(a[c * TILE]);
+                    o[size_t(c) * TILE] = folded[hf] ? o[size_t(c) * TILE] + x : x;
+                }
+                folded[hf] = true;
+                cnt[hf] = 0;
+            }
+        }
+        if (n_ev == 0) {
+            for (int c = 0; c < 2 * TILE; ++c) my[size_t(c) * TILE] = 0.0;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();          // no CTA leaves (or frees TMEM) while its peer may still signal it
+    if (warp == MMA_WARP) {
+        tc_fence_after();
+        tmem_dealloc2(tmem_base, TMEM_COLS);
+    }
+}
+
+// Sum the split partials in split order and scatter pair tile (BI, BJ) (and its mirror) into G.
+// Partial layout per (split, pair tile, rank): [half][col 128][row 128] doubles.
+__global__ void gram_ts2_reduce_kernel(const double* __restrict__ part, int tiles2, int splits, int nb2, int n, int accumulate,
+                                       double* __restrict__ G) {
+    int t = blockIdx.x >> 1, BI = 0;
+    const int rank = blockIdx.x & 1;
+    while (t >= nb2 - BI) { t -= nb2 - BI; ++BI; }
+    const int BJ = BI + t;
+    constexpr int PER = 2 * TILE * TILE;
+    for (int e = blockIdx.y * blockDim.x + threadIdx.x; e < PER; e += gridDim.y * blockDim.x) {
+        const int lr = e % TILE, c = (e / TILE) % TILE, hf = e / (TILE * TILE);
+        const int i = BI * T2_ROWS + rank * TILE + lr;
+        const int j = BJ * T2_ROWS + 128 * (c >> 6) + 64 * hf + (c & 63);
+        if (i >= n || j >= n) continue;
+        if (BI == BJ && j < i) continue;
+        double s = 0.0;
+        for (int sp = 0; sp < splits; ++sp) s += part[(size_t(sp) * tiles2 + (blockIdx.x >> 1)) * (2 * PER) + size_t(rank) * PER + e];
+        if (accumulate) {
+            G[size_t(i) * n + j] += s;
+            if (i != j) G[size_t(j) * n + i] += s;
+        } else {
+            G[size_t(i) * n + j] = s;
+            if (i != j) G[size_t(j) * n + i] = s;
+        }
+    }
+}

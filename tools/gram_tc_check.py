@@ -70,14 +70,15 @@ if __name__ == "__main__":
         sys.exit(0)
     if "--peak" in sys.argv:
         tf32_peak()
-    for n, segs in [(64, [4096]), (128, [32]), (128, [256 * 40]), (65, [3000]), (130, [2049 - 1, 1]), (200, [777 + 3, 64, 5000]),
+    IMPLS = [a for a in sys.argv[1:] if a in ("tc", "ss", "ts", "ts2", "ffma")] or ["tc", "ss", "ts2", "ffma"]
+    for n, segs in [(64, [4096]), (257, [4096 + 32]), (600, [5000, 77, 130000]), (128, [32]), (128, [256 * 40]), (65, [3000]), (130, [2049 - 1, 1]), (200, [777 + 3, 64, 5000]),
                     (300, [100000]), (1000, [70000, 36, 30000])]:
-        for impl in ("tc", "ts", "ffma"):
+        for impl in IMPLS:
             eg, ed = check(n, segs, impl)
             bad += (ed > 1e-5) or not np.isfinite(ed)
     if "--time" in sys.argv:
         timing(1000, 3_125_000, "tc")
-        timing(1000, 3_125_000, "ts")
+        timing(1000, 3_125_000, "ss")
         timing(500, 3_125_000, "tc")
         timing(128, 3_125_000, "tc")
         timing(1000, 3_125_000, "ffma", reps=1)
