@@ -26,6 +26,7 @@
 // warp arrivals) live in the leader CTA (rank 0) whose MMA warp issues every MMA; EMPTY[st] and
 // TFULL[region] are per CTA and signalled by multicast tcgen05.commit.
 #pragma once
+#include <type_traits>
 
 constexpr int T2_ROWS = 256;                          // pair-tile edge
 constexpr int T2_BTILE_BYTES = 64 * BK * 4;           // one B operand tile: 64 rows x 32 K = 8 KB
@@ -38,6 +39,7 @@ constexpr int T2_BAR_OFF = T2_SLOTS * T2_SLOT_BYTES + T2_ACC_BYTES;
 constexpr int T2_SMEM_BYTES = T2_BAR_OFF + 1024 + 256;
 constexpr int T2_CHUNK = KC_BLOCKS;                   // k-blocks per first-level chunk (KC = 256 columns)
 constexpr uint32_t IDESC2 = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(128 >> 3) << 17) | (uint32_t(256 >> 4) << 24);
+static_assert(T2_BTILE_BYTES == 8192, "the predicated B store hard-codes the hi -> lo tile distance");
 static_assert(T2_SMEM_BYTES <= 232448, "shared memory budget");
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -94,6 +96,67 @@ __device__ __forceinline__ uint64_t sub2(uint64_t a, uint64_t b) {
     uint64_t r;
     asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
     return r;
+}
+
+
+// One k-block of a producer thread as fp32 PAIRS (value pair g = columns 8q + 2g, 8q + 2g + 1):
+// 256-bit / 128-bit loads straight into 64-bit registers, so the packed subtracts need no moves.
+struct T2Regs {
+    uint64_t a[2][4], b[2][4], c[4];
+};
+__device__ __forceinline__ void ldg_pairs8(const float* p, uint64_t (&v)[4]) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.b64 {%0,%1,%2,%3}, [%4];" : "=l"(v[0]), "=l"(v[1]), "=l"(v[2]), "=l"(v[3]) : "l"(p));
+}
+__device__ __forceinline__ void ldg_pairs44(const float* p, uint64_t (&v)[4]) {
+    asm volatile("ld.global.nc.L1::no_allocate.v2.b64 {%0,%1}, [%2];" : "=l"(v[0]), "=l"(v[1]) : "l"(p));
+    asm volatile("ld.global.nc.L1::no_allocate.v2.b64 {%0,%1}, [%2];" : "=l"(v[2]), "=l"(v[3]) : "l"(p + 4));
+}
+__device__ __forceinline__ void t2_load(const KbIter& it, const TsRows& rows, bool diag, int q, T2Regs& r) {
+    const int64_t col = it.c0 + it.ks + q * 8;
+    const int rem = it.len - it.ks - q * 8;
+    if (rem >= 8) {
+        if (rows.v8) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) ldg_pairs8(rows.a[h] + col, r.a[h]);
+            if (!diag) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) ldg_pairs8(rows.b[h] + col, r.b[h]);
+            }
+        } else {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) ldg_pairs44(rows.a[h] + col, r.a[h]);
+            if (!diag) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) ldg_pairs44(rows.b[h] + col, r.b[h]);
+            }
+        }
+        if (rows.cbase) {
+            const float* cp = rows.cbase + col;
+            if ((reinterpret_cast<uintptr_t>(cp) & 15) == 0) {
+                asm volatile("ld.global.nc.v2.b64 {%0,%1}, [%2];" : "=l"(r.c[0]), "=l"(r.c[1]) : "l"(cp));
+                asm volatile("ld.global.nc.v2.b64 {%0,%1}, [%2];" : "=l"(r.c[2]), "=l"(r.c[3]) : "l"(cp + 4));
+            } else {
+#pragma unroll
+                for (int g = 0; g < 4; ++g) r.c[g] = pack2(__ldg(cp + 2 * g), __ldg(cp + 2 * g + 1));
+            }
+        } else {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) r.c[g] = 0ull;
+        }
+    } else {
+        auto part = [&](const float* row, uint64_t (&v)[4]) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+                v[g] = pack2((row && 2 * g < rem) ? __ldg(row + col + 2 * g) : 0.f, (row && 2 * g + 1 < rem) ? __ldg(row + col + 2 * g + 1) : 0.f);
+        };
+#pragma unroll
+        for (int h = 0; h < 2; ++h) part(rows.a[h], r.a[h]);
+        if (!diag) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) part(rows.b[h], r.b[h]);
+        }
+        part(rows.cbase, r.c);
+    }
 }
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
@@ -185,11 +248,11 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
         };
         KbIter it;
         it.init(v, u0, u1);
-        TsRegs r0, r1;
-        auto fetch = [&](TsRegs& r) {
+        T2Regs r0, r1;
+        auto fetch = [&](T2Regs& r) {
             if (it.valid()) {
                 if (it.p != cur_p) refresh_rows(it.p);
-                ts_load(it, rows, diag, q, r);
+                t2_load(it, rows, diag, q, r);
                 it.next(v);
             }
         };
@@ -200,7 +263,17 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
         const uint32_t a_lane = tmem_base + (uint32_t(lane0) << 16) + T2_TMEM_A0;
         const uint32_t full_leader = map_to_cta(FULL(0), 0);
         constexpr uint64_t HI2 = 0xffffe000ffffe000ull;
-        auto emit = [&](const TsRegs& r) {
+        const bool pad_any = !(okA[0] && okA[1] && okB[0] && okB[1]);
+        auto emit = [&](T2Regs& r, auto diag_c) {
+            constexpr bool DIAG = decltype(diag_c)::value;
+            if (pad_any) {   // padding rows: x := c, so the centred value is exactly zero (A is stored unconditionally)
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                    if (!okA[h]) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) r.a[h][g] = r.c[g];
+                    }
+            }
 #pragma unroll
             for (int sub = 0; sub < 2; ++sub) {
                 // this stage's two k-steps are value pairs g = sub and g = sub + 2 of the thread's 8 columns
@@ -208,17 +281,17 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
                     const int g = sub + 2 * j;
-                    const uint64_t c2 = pack2(r.c[2 * g], r.c[2 * g + 1]);
+                    const uint64_t c2 = r.c[g];
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        const uint64_t ta = okA[h] ? sub2(pack2(r.a[h][2 * g], r.a[h][2 * g + 1]), c2) : 0ull;
+                        const uint64_t ta = sub2(r.a[h][g], c2);
                         ah[h][j] = ta & HI2;
                         al[h][j] = sub2(ta, ah[h][j]);
-                        if (diag) {
+                        if constexpr (DIAG) {
                             bh[h][j] = ah[h][j];
                             bl[h][j] = al[h][j];
                         } else {
-                            const uint64_t tb = sub2(pack2(r.b[h][2 * g], r.b[h][2 * g + 1]), c2);
+                            const uint64_t tb = sub2(r.b[h][g], c2);
                             bh[h][j] = tb & HI2;
                             bl[h][j] = sub2(tb, bh[h][j]);
                         }
@@ -248,10 +321,11 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
                         const uint64_t vh = odd ? bh[h][1 - i] : bh[h][i], vl = odd ? bl[h][1 - i] : bl[h][i];
                         const int ge = sub + 2 * i, go = sub + 2 * (1 - i);
                         const uint32_t addr = sb + ((boff + h * 1024u) ^ (odd ? uint32_t(go) << 5 : uint32_t(ge) << 5));
-                        if (okB[h]) {
-                            asm volatile("st.shared.b64 [%0], %1;" ::"r"(addr), "l"(vh) : "memory");
-                            asm volatile("st.shared.b64 [%0], %1;" ::"r"(addr + T2_BTILE_BYTES), "l"(vl) : "memory");
-                        }
+                        asm volatile(
+                            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t"
+                            "@p st.shared.b64 [%0], %1;\n\t"
+                            "@p st.shared.b64 [%0+8192], %2;\n\t}" ::"r"(addr), "l"(vh), "l"(vl), "r"(uint32_t(okB[h]))
+                            : "memory");
                     }
                 }
                 tmem_wait_st();
@@ -262,14 +336,17 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
                 if (++stage == T2_NSTG) { stage = 0; phase ^= 1; }
             }
         };
-        for (int kb = 0; kb < nkb; kb += 2) {
-            emit(r0);
-            fetch(r0);
-            if (kb + 1 < nkb) {
-                emit(r1);
-                fetch(r1);
+        auto run = [&](auto diag_c) {
+            for (int kb = 0; kb < nkb; kb += 2) {
+                emit(r0, diag_c);
+                fetch(r0);
+                if (kb + 1 < nkb) {
+                    emit(r1, diag_c);
+                    fetch(r1);
+                }
             }
-        }
+        };
+        if (diag) run(std::true_type{}); else run(std::false_type{});
     } else if (warp == MMA_WARP) {
         // ================================ MMA issuer (leader CTA only) ================================
         if (rank == 0) {
