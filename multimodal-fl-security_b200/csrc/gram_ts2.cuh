@@ -39,6 +39,9 @@ constexpr int T2_BAR_OFF = T2_SLOTS * T2_SLOT_BYTES + T2_ACC_BYTES;
 constexpr int T2_SMEM_BYTES = T2_BAR_OFF + 1024 + 256;
 constexpr int T2_CHUNK = KC_BLOCKS;                   // k-blocks per first-level chunk (KC = 256 columns)
 constexpr uint32_t IDESC2 = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(128 >> 3) << 17) | (uint32_t(256 >> 4) << 24);
+// Register budget: 13 warps x 128 at launch; the epilogue warps hand back 88 each, the producers take 44.
+constexpr int T2_EPI_REGS = 40, T2_PROD_REGS = 168;
+static_assert((128 - T2_EPI_REGS) * EPI_WARPS >= (T2_PROD_REGS - 128) * PROD_WARPS, "setmaxnreg budget");
 static_assert(T2_BTILE_BYTES == 8192, "the predicated B store hard-codes the hi -> lo tile distance");
 static_assert(T2_SMEM_BYTES <= 232448, "shared memory budget");
 
@@ -203,7 +206,7 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
 
     if (warp >= EPI_WARPS && warp < MMA_WARP) {
         // ================================ producers ================================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(TS_PROD_REGS));
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(T2_PROD_REGS));
         const int qd = warp & 3, h16 = (warp - EPI_WARPS) >> 2;
         const int lane0 = 32 * qd + 16 * h16;           // first TMEM lane = first local row of this warp
         const int r8 = lane >> 2, q = lane & 3;
@@ -248,7 +251,7 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
         };
         KbIter it;
         it.init(v, u0, u1);
-        T2Regs r0, r1;
+        T2Regs r0, r1, r2;   // three k-blocks of loads in flight per thread
         auto fetch = [&](T2Regs& r) {
             if (it.valid()) {
                 if (it.p != cur_p) refresh_rows(it.p);
@@ -258,6 +261,7 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
         };
         fetch(r0);
         fetch(r1);
+        fetch(r2);
         int stage = 0;
         uint32_t phase = 1;
         const uint32_t a_lane = tmem_base + (uint32_t(lane0) << 16) + T2_TMEM_A0;
@@ -337,12 +341,16 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
             }
         };
         auto run = [&](auto diag_c) {
-            for (int kb = 0; kb < nkb; kb += 2) {
+            for (int kb = 0; kb < nkb; kb += 3) {
                 emit(r0, diag_c);
                 fetch(r0);
                 if (kb + 1 < nkb) {
                     emit(r1, diag_c);
                     fetch(r1);
+                }
+                if (kb + 2 < nkb) {
+                    emit(r2, diag_c);
+                    fetch(r2);
                 }
             }
         };
@@ -407,7 +415,7 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
         }
     } else {
         // ================================ epilogue ================================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TS_EPI_REGS));
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(T2_EPI_REGS));
         const int row = warp * 32 + lane;
         const uint32_t lane_base = tmem_base + (uint32_t(warp * 32) << 16);
         double* my = part + ((size_t(blockIdx.y) * (gridDim.x >> 1) + (blockIdx.x >> 1)) * 2 + rank) * (2 * TILE * TILE) + row;
