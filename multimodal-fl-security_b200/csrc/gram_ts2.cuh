@@ -82,6 +82,16 @@ __device__ __forceinline__ void umma2_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, 
         "r"(a_tmem), "l"(b_desc), "r"(IDESC2), "r"(accumulate)
         : "memory");
 }
+// same, the shared-memory descriptor passed as its two 32-bit words (the high word is a constant:
+// SBO = 1024 B, version 1, SWIZZLE_128B; only the start-address field of the low word moves)
+constexpr uint32_t DESC_HI = uint32_t((uint64_t(1024 >> 4) << 32 | uint64_t(1) << 46 | uint64_t(2) << 61) >> 32);
+__device__ __forceinline__ void umma2_tf32_ts_lohi(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t b_hi, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 bd;\n\tsetp.ne.b32 p, %5, 0;\n\tmov.b64 bd, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], bd, %4, p;\n\t}" ::"r"(d_tmem),
+        "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(IDESC2), "r"(accumulate)
+        : "memory");
+}
 // arrive (count 1) on the barrier at this shared::cta offset in BOTH CTAs of the pair once all
 // prior MMAs of this thread have completed
 __device__ __forceinline__ void umma2_commit_both(uint32_t bar) {
@@ -90,6 +100,13 @@ __device__ __forceinline__ void umma2_commit_both(uint32_t bar) {
                  : "memory");
 }
 
+// one lane of a converged warp (elect.sync); the compiler keeps warp-uniform operands of the
+// guarded tcgen05 instructions in uniform registers instead of re-broadcasting them per MMA
+__device__ __forceinline__ bool elect_one() {
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\tselp.u32 %0, 1, 0, q;\n\t}" : "=r"(p));
+    return p != 0;
+}
 __device__ __forceinline__ uint64_t pack2(float a, float b) {
     uint64_t r;
     asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
@@ -360,6 +377,8 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
         if (rank == 0) {
             int s = 0;
             uint32_t full_phase = 0;
+            const uint32_t blo0 = uint32_t(make_desc(sbase));      // low descriptor word of slot 0, half 0, hi tile, k-step 0
+            const uint32_t a_tm0 = tmem_base + T2_TMEM_A0;
             uint32_t tempty_uses = 0;          // bit r: parity of the next wait on TEMPTY[r]
             int reg[2] = {1, 0};               // accumulator region of half 0 / half 1
             bool fresh[2] = {true, true};      // next MMA of the half starts a chunk (overwrite)
@@ -369,23 +388,28 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
                 for (int sub = 0; sub < 2; ++sub) {
                     mbar_wait_cluster(FULL(s), full_phase);
                     tc_fence_after();
-                    if (lane == 0) {
-                        const uint32_t slot = sbase + uint32_t(s >> 1) * T2_SLOT_BYTES;
-                        const uint32_t a_hi = tmem_base + T2_TMEM_A0 + uint32_t(s * 32), a_lo = a_hi + 16;
+                    {
+                        // descriptor low words: start address (>> 4) advances by 2 per 32-byte k-step
+                        const uint32_t lo0 = blo0 + uint32_t(s >> 1) * (T2_SLOT_BYTES >> 4) + uint32_t(sub) * 2u;
+                        const uint32_t a_hi = a_tm0 + uint32_t(s * 32);
+                        const uint32_t d0 = tmem_base + uint32_t(reg[0] * TILE), d1 = tmem_base + uint32_t(reg[1] * TILE);
+                        const uint32_t acc0 = fresh[0] ? 0u : 1u, acc1 = fresh[1] ? 0u : 1u;
+                        const uint32_t empty_s = EMPTY(s);
+                        if (elect_one()) {
 #pragma unroll
-                        for (int j = 0; j < 2; ++j) {
-                            const uint32_t ko = uint32_t(sub + 2 * j) * 32u;   // k-step g = sub + 2j: bytes inside the 128-byte row
+                            for (int j = 0; j < 2; ++j) {
 #pragma unroll
-                            for (int hf = 0; hf < 2; ++hf) {
-                                const uint32_t d = tmem_base + uint32_t(reg[hf] * TILE);
-                                const uint32_t b_hi = slot + uint32_t(hf) * (2u * T2_BTILE_BYTES) + ko, b_lo = b_hi + T2_BTILE_BYTES;
-                                umma2_tf32_ts(d, a_hi + 8 * j, make_desc(b_hi), fresh[hf] ? 0u : 1u);
-                                umma2_tf32_ts(d, a_hi + 8 * j, make_desc(b_lo), 1u);
-                                umma2_tf32_ts(d, a_lo + 8 * j, make_desc(b_hi), 1u);
-                                fresh[hf] = false;
+                                for (int hf = 0; hf < 2; ++hf) {
+                                    const uint32_t d = hf ? d1 : d0;
+                                    const uint32_t b_hi = lo0 + uint32_t(4 * j + hf * (2 * T2_BTILE_BYTES >> 4)), b_lo = b_hi + (T2_BTILE_BYTES >> 4);
+                                    umma2_tf32_ts_lohi(d, a_hi + 8 * j, b_hi, DESC_HI, j == 0 ? (hf ? acc1 : acc0) : 1u);
+                                    umma2_tf32_ts_lohi(d, a_hi + 8 * j, b_lo, DESC_HI, 1u);
+                                    umma2_tf32_ts_lohi(d, a_hi + 16 + 8 * j, b_hi, DESC_HI, 1u);
+                                }
                             }
+                            umma2_commit_both(empty_s);
                         }
-                        umma2_commit_both(EMPTY(s));
+                        fresh[0] = fresh[1] = false;
                     }
                     __syncwarp();
                     if (++s == T2_NSTG) { s = 0; full_phase ^= 1; }
@@ -397,7 +421,7 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
                 else if (done % (T2_CHUNK / 2) == 0) nclose = 1;
                 for (int c = 0; c < nclose; ++c) {
                     const int hf = (ev + 1) & 1, r = ev % 3;
-                    if (lane == 0) umma2_commit_both(TFULL(r));
+                    if (elect_one()) umma2_commit_both(TFULL(r));
                     __syncwarp();
                     if (done < nkb) {
                         // the half continues in region (ev + 2) % 3, which event ev - 1 drained
