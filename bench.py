@@ -223,7 +223,7 @@ def extra_defenses(rank, world, dist_on, group):
     gk["TFLOPs_alg"] = world * n4 * (n4 + 1) * d4 / (gk["ms"] / 1e3) / 1e12
     gk["roofline"] = {"bound": "tensor", "achieved": gk["TFLOPs_alg"] / world, "peak": tf32 / 3.0, "unit": "TFLOP/s",
                       "frac": gk["TFLOPs_alg"] / world / (tf32 / 3.0), "tf32_dense_measured": tf32,
-                      "kernel": "gram_tc_kernel (tcgen05 kind::tf32, 3 products per k-step)"}
+                      "kernel": "gram_ts2_kernel (tcgen05 cta_group::2 kind::tf32, 256x256 CTA-pair tiles, A from TMEM, 3 products per k-step)"}
     return out
 
 

@@ -12,5 +12,5 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
     python bench.py --steps 3 --warmup 3 --no-extras --no-cpu --no-e2e > gpurun_out/ncu_launch.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:colselect_ -s 3 -c 1 -o gpurun_out/k1_full -f \
     python bench.py --steps 3 --warmup 3 --no-extras --no-cpu --no-e2e > gpurun_out/ncu_full.log 2>&1
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:gram_tc_kernel -s 1 -c 1 -o gpurun_out/k4_full -f python tools/gram_tc_check.py --only-time > gpurun_out/ncu_k4.log 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:gram_ts2_kernel -s 1 -c 1 -o gpurun_out/k4_full -f python tools/gram_tc_check.py --only-time > gpurun_out/ncu_k4.log 2>&1
 ls -la gpurun_out
