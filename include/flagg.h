@@ -135,6 +135,10 @@ int flagg_colwise_select_host(int n, int P, const int64_t* seg_numel,
                               const void* const* host_seg_ptrs, int mode, int k,
                               float* host_out, int64_t chunk_cols);
 
+/* The host path keeps its device staging buffers, streams and events between calls (a
+ * federated round repeats the same shapes); this frees them.  Always returns FLAGG_OK. */
+int flagg_host_release(void);
+
 /* Copy n host rows (P segments each) into one dense device matrix dst[n, ld]
  * (ld >= d, fp32), chunked and asynchronous on `stream`.  Used to make host inputs
  * resident for the two-pass defenses (Krum, FLTrust, clipping). */

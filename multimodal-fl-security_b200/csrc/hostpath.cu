@@ -3,7 +3,13 @@
 // through the GPU in chunks, H2D copies of chunk c+1 overlapping the select kernel and
 // the D2H copy of chunk c (two internal streams, three staging buffers).  PCIe-bound by
 // construction; reported separately from the HBM roofline (bench.py "e2e").
+// The staging buffers, streams, events and views are kept between calls (one cached pipe per
+// process, rebuilt when n / chunk width / device change, freed by flagg_host_release()):
+// a federated round calls this once per round with the same shapes.  Rows that sit at a uniform
+// pitch in host memory (one [n x d] matrix) move with ONE 2-D copy per chunk and segment.
 #include <algorithm>
+#include <cstring>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -15,21 +21,28 @@ struct HostPipe {
     static constexpr int NBUF = 3;
     float* stage[NBUF] = {nullptr, nullptr, nullptr};
     float* outb[NBUF] = {nullptr, nullptr, nullptr};
+    float* hout[NBUF] = {nullptr, nullptr, nullptr};   // pinned bounce buffers for pageable outputs
+    int64_t pend_c0[NBUF] = {0, 0, 0}, pend_w[NBUF] = {0, 0, 0};   // result chunk waiting in hout[b]
     flagg_view* view[NBUF] = {nullptr, nullptr, nullptr};
     cudaEvent_t filled[NBUF] = {}, drained[NBUF] = {};
     cudaStream_t s_copy = nullptr, s_comp = nullptr;
     bool ev_ok = false;
+    int n = 0, device = -1, nbuf = 0;
+    int64_t chunk_cols = 0;
     ~HostPipe() {
         for (int b = 0; b < NBUF; ++b) {
             if (view[b]) flagg_view_destroy(view[b]);
             if (stage[b]) cudaFree(stage[b]);
             if (outb[b]) cudaFree(outb[b]);
+            if (hout[b]) cudaFreeHost(hout[b]);
             if (ev_ok) { cudaEventDestroy(filled[b]); cudaEventDestroy(drained[b]); }
         }
         if (s_copy) cudaStreamDestroy(s_copy);
         if (s_comp) cudaStreamDestroy(s_comp);
     }
 };
+
+HostPipe* g_pipe = nullptr;   // cached between calls; intentionally not destroyed at process exit
 
 int make_dense_view(flagg_view** out, float* base, int n, int64_t ld, int64_t cols, cudaStream_t st) {
     std::vector<const void*> ptrs(n);
@@ -58,33 +71,80 @@ int flagg_colwise_select_host(int n, int P, const int64_t* seg_numel, const void
     chunk_cols = std::min<int64_t>((chunk_cols + 127) & ~int64_t(127), (d + 127) & ~int64_t(127));
     const int64_t nchunks = (d + chunk_cols - 1) / chunk_cols;
 
-    HostPipe hp;
-    FLAGG_CUDA(cudaStreamCreateWithFlags(&hp.s_copy, cudaStreamNonBlocking));
-    FLAGG_CUDA(cudaStreamCreateWithFlags(&hp.s_comp, cudaStreamNonBlocking));
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);   // one host-path call at a time per process (it owns the copy engines anyway)
+    int device = 0;
+    FLAGG_CUDA(cudaGetDevice(&device));
     const int nbuf = int(std::min<int64_t>(HostPipe::NBUF, nchunks));
-    for (int b = 0; b < HostPipe::NBUF; ++b) {
-        FLAGG_CUDA(cudaEventCreateWithFlags(&hp.filled[b], cudaEventDisableTiming));
-        FLAGG_CUDA(cudaEventCreateWithFlags(&hp.drained[b], cudaEventDisableTiming));
+    if (g_pipe && (g_pipe->n != n || g_pipe->chunk_cols != chunk_cols || g_pipe->device != device || g_pipe->nbuf < nbuf)) {
+        delete g_pipe;
+        g_pipe = nullptr;
     }
-    hp.ev_ok = true;
-    for (int b = 0; b < nbuf; ++b) {
-        FLAGG_CUDA(cudaMalloc(&hp.stage[b], sizeof(float) * size_t(n) * chunk_cols));
-        FLAGG_CUDA(cudaMalloc(&hp.outb[b], sizeof(float) * size_t(chunk_cols)));
-        int rc = make_dense_view(&hp.view[b], hp.stage[b], n, chunk_cols, chunk_cols, hp.s_comp);
-        if (rc != FLAGG_OK) return rc;
+    if (!g_pipe) {
+        HostPipe* np = new HostPipe;
+        np->n = n; np->chunk_cols = chunk_cols; np->device = device; np->nbuf = nbuf;
+        auto build = [&]() -> int {
+            FLAGG_CUDA(cudaStreamCreateWithFlags(&np->s_copy, cudaStreamNonBlocking));
+            FLAGG_CUDA(cudaStreamCreateWithFlags(&np->s_comp, cudaStreamNonBlocking));
+            for (int b = 0; b < HostPipe::NBUF; ++b) {
+                FLAGG_CUDA(cudaEventCreateWithFlags(&np->filled[b], cudaEventDisableTiming));
+                FLAGG_CUDA(cudaEventCreateWithFlags(&np->drained[b], cudaEventDisableTiming));
+            }
+            np->ev_ok = true;
+            for (int b = 0; b < nbuf; ++b) {
+                FLAGG_CUDA(cudaMalloc(&np->stage[b], sizeof(float) * size_t(n) * chunk_cols));
+                FLAGG_CUDA(cudaMalloc(&np->outb[b], sizeof(float) * size_t(chunk_cols)));
+                FLAGG_CUDA(cudaHostAlloc(&np->hout[b], sizeof(float) * size_t(chunk_cols), cudaHostAllocDefault));
+                int rc = make_dense_view(&np->view[b], np->stage[b], n, chunk_cols, chunk_cols, np->s_comp);
+                if (rc != FLAGG_OK) return rc;
+            }
+            return FLAGG_OK;
+        };
+        int rc = build();
+        if (rc != FLAGG_OK) { delete np; return rc; }
+        g_pipe = np;
+    }
+    HostPipe& hp = *g_pipe;
+    bool out_pinned = false;
+    {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, host_out) == cudaSuccess) out_pinned = (at.type == cudaMemoryTypeHost);
+        else (void)cudaGetLastError();
+    }
+    // per segment: do the n rows sit at one pitch in host memory?
+    std::vector<int64_t> pitch(P, 0);
+    for (int p = 0; p < P; ++p) {
+        if (n < 2) continue;
+        const char* b0 = static_cast<const char*>(host_seg_ptrs[p]);
+        const int64_t st = static_cast<const char*>(host_seg_ptrs[size_t(P) + p]) - b0;
+        bool ok = st >= int64_t(sizeof(float)) * seg_numel[p] && st > 0;
+        for (int i = 2; i < n && ok; ++i) ok = (static_cast<const char*>(host_seg_ptrs[size_t(i) * P + p]) - b0) == st * i;
+        pitch[p] = ok ? st : 0;
     }
     flagg_view* tail_view = nullptr;  // the last chunk is usually narrower
     int rc = FLAGG_OK;
     for (int64_t ch = 0; ch < nchunks && rc == FLAGG_OK; ++ch) {
         const int b = int(ch % nbuf);
         const int64_t c0 = ch * chunk_cols, c1 = std::min(d, c0 + chunk_cols), w = c1 - c0;
-        if (ch >= nbuf) FLAGG_CUDA(cudaStreamWaitEvent(hp.s_copy, hp.drained[b], 0));
+        if (ch >= nbuf) {
+            FLAGG_CUDA(cudaStreamWaitEvent(hp.s_copy, hp.drained[b], 0));
+            if (!out_pinned) {   // the chunk that used this buffer last has landed in hout[b]: hand it to the caller
+                FLAGG_CUDA(cudaEventSynchronize(hp.drained[b]));
+                memcpy(host_out + hp.pend_c0[b], hp.hout[b], sizeof(float) * size_t(hp.pend_w[b]));
+            }
+        }
         // first segment overlapping [c0, c1)
         int p0 = int(std::upper_bound(seg_start.begin(), seg_start.end(), c0) - seg_start.begin()) - 1;
-        for (int i = 0; i < n; ++i) {
-            for (int p = p0; p < P && seg_start[p] < c1; ++p) {
-                const int64_t a = std::max(c0, seg_start[p]), e = std::min(c1, seg_start[p + 1]);
-                if (e <= a) continue;
+        for (int p = p0; p < P && seg_start[p] < c1; ++p) {
+            const int64_t a = std::max(c0, seg_start[p]), e = std::min(c1, seg_start[p + 1]);
+            if (e <= a) continue;
+            if (pitch[p] > 0) {
+                const float* src = static_cast<const float*>(host_seg_ptrs[p]) + (a - seg_start[p]);
+                FLAGG_CUDA(cudaMemcpy2DAsync(hp.stage[b] + (a - c0), sizeof(float) * size_t(chunk_cols), src, size_t(pitch[p]),
+                                             sizeof(float) * size_t(e - a), size_t(n), cudaMemcpyHostToDevice, hp.s_copy));
+                continue;
+            }
+            for (int i = 0; i < n; ++i) {
                 const float* src = static_cast<const float*>(host_seg_ptrs[size_t(i) * P + p]) + (a - seg_start[p]);
                 FLAGG_CUDA(cudaMemcpyAsync(hp.stage[b] + size_t(i) * chunk_cols + (a - c0), src,
                                            sizeof(float) * size_t(e - a), cudaMemcpyHostToDevice, hp.s_copy));
@@ -100,16 +160,32 @@ int flagg_colwise_select_host(int n, int P, const int64_t* seg_numel, const void
         }
         rc = flagg_colwise_select(use, mode, k, hp.outb[b], hp.s_comp);
         if (rc != FLAGG_OK) break;
-        FLAGG_CUDA(cudaMemcpyAsync(host_out + c0, hp.outb[b], sizeof(float) * size_t(w), cudaMemcpyDeviceToHost, hp.s_comp));
+        // a D2H copy into pageable memory blocks this thread per chunk and stalls the H2D queue: go through pinned bounce buffers
+        FLAGG_CUDA(cudaMemcpyAsync(out_pinned ? host_out + c0 : hp.hout[b], hp.outb[b], sizeof(float) * size_t(w), cudaMemcpyDeviceToHost, hp.s_comp));
+        hp.pend_c0[b] = c0;
+        hp.pend_w[b] = w;
         FLAGG_CUDA(cudaEventRecord(hp.drained[b], hp.s_comp));
     }
     cudaError_t e1 = cudaStreamSynchronize(hp.s_copy), e2 = cudaStreamSynchronize(hp.s_comp);
+    if (rc == FLAGG_OK && e1 == cudaSuccess && e2 == cudaSuccess && !out_pinned)
+        for (int64_t ch = std::max<int64_t>(0, nchunks - nbuf); ch < nchunks; ++ch) {
+            const int b = int(ch % nbuf);
+            memcpy(host_out + hp.pend_c0[b], hp.hout[b], sizeof(float) * size_t(hp.pend_w[b]));
+        }
     if (tail_view) flagg_view_destroy(tail_view);
     if (rc != FLAGG_OK) return rc;
     if (e1 != cudaSuccess || e2 != cudaSuccess) {
         set_error("flagg_colwise_select_host: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
         return FLAGG_ECUDA;
     }
+    return FLAGG_OK;
+}
+
+int flagg_host_release(void) {
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    delete g_pipe;
+    g_pipe = nullptr;
     return FLAGG_OK;
 }
 

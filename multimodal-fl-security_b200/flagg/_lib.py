@@ -45,6 +45,7 @@ def lib():
         "flagg_krum_scores": (i32, [vp, i32, i32, vp, vp, vp]),
         "flagg_colwise_select_host": (i32, [i32, i32, C.POINTER(i64), C.POINTER(vp), i32, i32, vp, i64]),
         "flagg_upload_rows": (i32, [i32, i32, C.POINTER(i64), C.POINTER(vp), vp, i64, vp]),
+        "flagg_host_release": (i32, []),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)          # AttributeError here = header/library mismatch
@@ -55,7 +56,7 @@ def lib():
 
 EXPORTS = ["flagg_version", "flagg_last_error", "flagg_device_info", "flagg_view_create", "flagg_view_destroy",
            "flagg_view_cols", "flagg_view_rows", "flagg_colwise_select", "flagg_row_reduce", "flagg_row_combine",
-           "flagg_gram", "flagg_krum_scores", "flagg_colwise_select_host", "flagg_upload_rows"]
+           "flagg_gram", "flagg_krum_scores", "flagg_colwise_select_host", "flagg_upload_rows", "flagg_host_release"]
 
 
 def check(rc: int, what: str) -> None:

@@ -322,6 +322,26 @@ def test_host_path_equals_device_path():
     ud.close()
 
 
+def test_host_path_uniform_pitch_rows_cached_pipe_and_release():
+    """Host rows that are views of ONE pinned matrix move with 2-D copies; the staging pipe is
+    reused across calls (same shapes), rebuilt when n changes, and freed by flagg_host_release."""
+    from flagg import MEDIAN, TRIMMED_MEAN, engine
+    from flagg._lib import lib
+    rng = np.random.RandomState(6)
+    for n, d in ((20, 300_001), (20, 300_001), (33, 150_000)):
+        X = rows_model(rng, n, d, byz=3)
+        host = torch.from_numpy(X).pin_memory()
+        offs = [0, 1000, 1000 + 77, d]
+        uh = engine.Updates([[host[i, offs[p]:offs[p + 1]] for p in range(3)] for i in range(n)])
+        ud = engine.Updates(dev_lists(X, [offs[p + 1] - offs[p] for p in range(3)]))
+        for mode, k in ((MEDIAN, 0), (TRIMMED_MEAN, 3)):
+            a = engine.colwise_select(ud, mode, k).cpu().numpy()
+            b = engine.colwise_select(uh, mode, k)
+            assert not b.is_cuda and np.array_equal(bits(a), bits(b.numpy()))
+        ud.close()
+    assert lib().flagg_host_release() == 0 and lib().flagg_host_release() == 0
+
+
 def test_errors_surface_as_exceptions():
     from flagg import FlaggError, TRIMMED_MEAN, engine
     from src.defenses import KrumDefense, get_defense
