@@ -26,6 +26,8 @@ struct NetEntry { int n; colselect_launch_fn fn; };
 static const NetEntry g_nets[] = {FLAGG_NET_SIZES(X)};
 #undef X
 
+int colselect_tile_launch(const flagg_view* v, int mode, int k, float* out, cudaStream_t st);   // colselect_tile.cu
+
 constexpr int RX_THREADS = 128;
 
 __device__ __forceinline__ unsigned f2ukey(float x) { return unsigned(f2key(x)) ^ 0x80000000u; }
@@ -161,6 +163,17 @@ extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float*
         const bool force_bulk = impl && !strcmp(impl, "bulk");
         const int flag = (want_bulk && exact && v->align_bytes >= 16 && (v->dense || force_bulk)) ? CS_BULK : 0;
         return e->fn(v->dev, variant | flag, k, out, units, sms, st);
+    }
+    {   // shared-memory tile select (colselect_tile.cu): one HBM read instead of 8-17.  Measured against the radix
+        // fallback (tools/k1_large_n.py, profiles/r01_k1_large_n.txt) it wins for the median up to n ~ 1500 and for
+        // the trimmed mean (three tile loads) from n ~ 400; FLAGG_K1_IMPL=tile|radix forces one.
+        const char* impl = getenv("FLAGG_K1_IMPL");
+        const bool force_tile = impl && !strcmp(impl, "tile"), force_radix = impl && !strcmp(impl, "radix");
+        const bool pick = (mode == FLAGG_MEDIAN) ? n <= 1500 : (n >= 400 && n <= 1500);
+        if (force_tile || (pick && !force_radix)) {
+            const int rc = colselect_tile_launch(v, mode, k, out, st);
+            if (rc != FLAGG_EUNSUPPORTED) return rc;
+        }
     }
     const size_t smem = sizeof(float*) * size_t(n) + sizeof(int) * 16 * RX_THREADS;
     FLAGG_REQUIRE(smem <= 200 * 1024, "flagg_colwise_select: n=%d too large", n);

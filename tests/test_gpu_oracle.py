@@ -101,9 +101,14 @@ def test_median_and_trimmed_dense_tma_path(n, impl, monkeypatch):
     u.close()
 
 
-@pytest.mark.parametrize("n", [129, 130, 200, 257, 1000])
-def test_median_radix_fallback(n):
+@pytest.mark.parametrize("impl", ["tile", "radix"])
+@pytest.mark.parametrize("n", [129, 130, 131, 200, 257, 1000, 2047])
+def test_median_large_n_tile_and_radix(n, impl, monkeypatch):
+    """n beyond the register networks: the shared-memory tile select (colselect_tile.cu, default)
+    and the old re-reading radix select (FLAGG_K1_IMPL=radix), bit-exact against the
+    (value, index)-ordered median incl. +-0 / NaN / Inf / duplicate columns and ragged tiles."""
     from flagg import MEDIAN
+    monkeypatch.setenv("FLAGG_K1_IMPL", impl)
     rng = np.random.RandomState(n)
     d = 300
     X = rows_model(rng, n, d, byz=n // 10)
@@ -114,9 +119,14 @@ def test_median_radix_fallback(n):
 
 
 @pytest.mark.parametrize("n,k", [(3, 1), (5, 1), (5, 2), (10, 1), (20, 2), (20, 4), (33, 9), (64, 6), (100, 10),
-                                 (100, 28), (128, 12), (129, 12), (300, 30), (1000, 100)])
-def test_trimmed_mean_vs_oracle(n, k):
+                                 (100, 28), (128, 12), (129, 12), (130, 64), (300, 30), (1000, 100), (1000, 499), (2047, 1)])
+@pytest.mark.parametrize("impl", ["auto", "tile", "radix"])
+def test_trimmed_mean_vs_oracle(n, k, impl, monkeypatch):
     from flagg import TRIMMED_MEAN
+    if impl != "auto":
+        if n <= 128:
+            pytest.skip("FLAGG_K1_IMPL=tile|radix only matters beyond the register networks")
+        monkeypatch.setenv("FLAGG_K1_IMPL", impl)
     rng = np.random.RandomState(7 * n + k)
     d = 1100 if n <= 128 else 260
     X = rows_model(rng, n, d, byz=min(k, n // 5))
@@ -130,6 +140,26 @@ def test_trimmed_mean_vs_oracle(n, k):
     # and against the FP64 statement, tighter: one rounding of the exact mean
     t64 = oracle64.trimmed_mean64(X, k)
     assert_close_scaled(got, t64, oracle64.trimmed_scale(X, k), tol=2e-7, what="fp64")
+
+
+def test_large_n_select_unaligned_views_and_all_equal_columns(monkeypatch):
+    """Tile select on rows that are 4-byte aligned views (4-byte cp.async path), with columns whose
+    values are all equal (no informative bit) and columns of exact duplicates around the median."""
+    from flagg import MEDIAN, TRIMMED_MEAN, engine
+    rng = np.random.RandomState(77)
+    n, d = 300, 1001
+    X = rows_model(rng, n, d, byz=30)
+    X[:, 5] = 0.125
+    X[:, 6] = -0.0
+    X[100:220, 7] = X[100, 7]
+    big = torch.from_numpy(X).cuda()                                  # pitch 1001 floats: rows 4-byte aligned only
+    u = engine.Updates([[big[i]] for i in range(n)])
+    monkeypatch.setenv("FLAGG_K1_IMPL", "tile")
+    got = engine.colwise_select(u, MEDIAN, 0).cpu().numpy()
+    assert np.array_equal(bits(got), bits(oracle64.median_stable(X)))
+    gt = engine.colwise_select(u, TRIMMED_MEAN, 30).cpu().numpy()
+    assert_close_scaled(gt, oracle64.trimmed_mean64(X, 30), oracle64.trimmed_scale(X, 30), tol=2e-7, what="tile trimmed")
+    u.close()
 
 
 def test_trimmed_mean_nan_kept_and_inf():
