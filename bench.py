@@ -287,7 +287,11 @@ def run_flagg(args, rank, world, local_rank):
         del host, host_lists, res
     u.close()
     del X, u
-    extras = extra_defenses(rank, world, dist_on, dist.group.WORLD if dist_on else None) if not args.no_extras else {}
+    # the sharded defenses' one collective goes through the C-ABI communicator (flagg_comm: NCCL), its id over torch.distributed
+    comm = engine.Comm.from_torch() if (dist_on and not args.no_extras) else None
+    extras = extra_defenses(rank, world, dist_on, comm) if not args.no_extras else {}
+    if comm is not None:
+        comm.close()
 
     if rank == 0:
         line = {

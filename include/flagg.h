@@ -53,7 +53,11 @@ typedef enum flagg_select_mode {
     FLAGG_TRIMMED_MEAN = 1   /* mean of sorted ranks [k, n-k)                     */
 } flagg_select_mode;
 
+typedef enum flagg_reduce_op { FLAGG_SUM = 0, FLAGG_MAX = 1 } flagg_reduce_op;
+
 typedef struct flagg_view flagg_view;
+typedef struct flagg_comm flagg_comm;
+#define FLAGG_UNIQUE_ID_BYTES 128
 
 /* ---- library ---------------------------------------------------------------- */
 int flagg_version(void);
@@ -144,6 +148,22 @@ int flagg_host_release(void);
  * resident for the two-pass defenses (Krum, FLTrust, clipping). */
 int flagg_upload_rows(int n, int P, const int64_t* seg_numel,
                       const void* const* host_seg_ptrs, float* dst, int64_t ld, void* stream);
+
+/* ---- parameter-sharded aggregation over several GPUs (one process per GPU) ---- */
+/* With the parameter dimension sharded, median / trimmed mean / FedAvg / weighted combine need no
+ * communication.  Krum all-reduces its partial n x n FP64 Gram (flagg_gram on the rank's columns,
+ * krum.py:73-99), FLTrust / clipping / norm bounding all-reduce the 2n+1 FP64 partial sums of
+ * flagg_row_reduce (SUM) and its n fp32 maxima (MAX) (fltrust.py:170-176,
+ * differential_privacy.py:225-230, 311); every rank then derives identical scores, selections and
+ * weights.  NCCL over NVLink; rank 0 creates the 128-byte id, the host program distributes it.
+ * The communicator is bound to the device current at flagg_comm_create; calls are stream-ordered. */
+int flagg_comm_unique_id(void* id128);
+int flagg_comm_create(flagg_comm** out, int nranks, int rank, const void* id128);
+int flagg_comm_destroy(flagg_comm* c);
+int flagg_comm_size(const flagg_comm* c);
+int flagg_comm_rank(const flagg_comm* c);
+int flagg_allreduce_f64(flagg_comm* c, double* buf, size_t count, int op, void* stream);
+int flagg_allreduce_f32(flagg_comm* c, float* buf, size_t count, int op, void* stream);
 
 #ifdef __cplusplus
 }

@@ -5,4 +5,4 @@ to this package) mirrors the reference's plugin classes on top of it.
 """
 from ._lib import FlaggError, LIB_PATH, MEDIAN, TRIMMED_MEAN, EXPORTS, lib  # noqa: F401
 from . import engine  # noqa: F401
-from .engine import Updates  # noqa: F401
+from .engine import Comm, Updates  # noqa: F401

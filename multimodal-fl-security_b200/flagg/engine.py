@@ -23,6 +23,70 @@ def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+class Comm:
+    """Native communicator of the C-ABI (flagg_comm: NCCL over NVLink), one per process / GPU.
+    The only collectives the parameter-sharded path has: the all-reduce of a partial FP64 Gram
+    matrix (Krum) and of partial row statistics (FLTrust, clipping, norm bounding).
+    ``Comm.from_torch()`` takes rank / world size from torch.distributed and lets rank 0's NCCL
+    id travel over that group (gloo or nccl); ``Comm(nranks, rank, id)`` takes them directly."""
+
+    def __init__(self, nranks: int, rank: int, unique_id: bytes):
+        _require_cuda()
+        if len(unique_id) != 128:
+            raise ValueError("the NCCL unique id is 128 bytes")
+        self._id = C.create_string_buffer(bytes(unique_id), 128)
+        h = C.c_void_p()
+        check(lib().flagg_comm_create(C.byref(h), int(nranks), int(rank), self._id), "flagg_comm_create")
+        self._h, self.nranks, self.rank = h, int(nranks), int(rank)
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        check(lib().flagg_comm_unique_id(buf), "flagg_comm_unique_id")
+        return buf.raw
+
+    @classmethod
+    def from_torch(cls, group=None) -> "Comm":
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        box = [cls.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        return cls(world, rank, box[0])
+
+    def all_reduce(self, t: torch.Tensor, op: str = "sum") -> torch.Tensor:
+        if not (t.is_cuda and t.is_contiguous()):
+            raise ValueError("all_reduce needs a contiguous device tensor")
+        code = {"sum": 0, "max": 1}[op]
+        if t.dtype == torch.float64:
+            check(lib().flagg_allreduce_f64(self._h, t.data_ptr(), t.numel(), code, _stream()), "flagg_allreduce_f64")
+        elif t.dtype == torch.float32:
+            check(lib().flagg_allreduce_f32(self._h, t.data_ptr(), t.numel(), code, _stream()), "flagg_allreduce_f32")
+        else:
+            raise ValueError(f"all_reduce: unsupported dtype {t.dtype}")
+        return t
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            lib().flagg_comm_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def all_reduce(t: torch.Tensor, group, op: str = "sum") -> torch.Tensor:
+    """In place over ``group``: a flagg ``Comm`` (native NCCL communicator) or a torch.distributed
+    process group (any backend -- the CPU tests drive the sharded host logic over gloo)."""
+    if isinstance(group, Comm):
+        return group.all_reduce(t, op)
+    import torch.distributed as dist
+    dist.all_reduce(t, op=dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX, group=group)
+    return t
+
+
 class Updates:
     """n client updates of P tensors each, as the defenses receive them
     (base_defense.py:31-35).  Device tensors are used in place; host tensors stay on the
@@ -172,9 +236,8 @@ def row_stats(u: Updates, g0_flat: Optional[torch.Tensor] = None, group=None, ce
         check(lib().flagg_row_reduce(u.view(), g_ptr, 1 if centered else 0, p, (p + 8 * n) if g_ptr else None, linf.data_ptr(),
                                      (p + 16 * n) if g_ptr else None, _stream()), "flagg_row_reduce")
         if group is not None:
-            import torch.distributed as dist
-            dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
-            dist.all_reduce(linf, op=dist.ReduceOp.MAX, group=group)
+            all_reduce(buf, group, "sum")
+            all_reduce(linf, group, "max")
         h = buf.cpu().numpy()
         return dict(sumsq=h[:n].copy(), dot=h[n:2 * n].copy(), g0_sumsq=float(h[2 * n]),
                     linf=linf.cpu().numpy())
@@ -234,8 +297,7 @@ def gram(u: Updates, center: Optional[torch.Tensor] = None, group=None, auto_cen
         check(lib().flagg_gram(u.view(), center.data_ptr() if center is not None else None, 0, G.data_ptr(),
                                _stream()), "flagg_gram")
         if group is not None:
-            import torch.distributed as dist
-            dist.all_reduce(G, op=dist.ReduceOp.SUM, group=group)
+            all_reduce(G, group, "sum")
     return G
 
 

@@ -1,7 +1,7 @@
 """BaseDefense / NoDefense -- mirrors /root/reference/src/defenses/base_defense.py:13-97.
 
 Engine knobs ride in the config dict as optional extra keys (ignored by the reference):
-  'process_group'  a torch.distributed group: the parameter dimension is sharded over its
+  'process_group'  a flagg.Comm (native NCCL communicator) or a torch.distributed group: the parameter dimension is sharded over its
                    ranks, each rank passes only its column shard, partial Gram matrices /
                    norms / dots are all-reduced (NCCL) before any selection.
 """

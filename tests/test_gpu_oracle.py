@@ -372,6 +372,32 @@ def test_host_path_uniform_pitch_rows_cached_pipe_and_release():
     assert lib().flagg_host_release() == 0 and lib().flagg_host_release() == 0
 
 
+def test_native_communicator_single_rank_and_errors():
+    """flagg_comm (NCCL through the C-ABI) with one rank: sum / max all-reduce are identities and
+    stream-ordered; sharded defenses accept it as 'process_group'.  The multi-rank check is
+    tools/comm_check.py under torchrun (profiles/r01_comm_check_n2.txt)."""
+    from flagg import Comm, FlaggError, engine
+    from src.defenses import KrumDefense
+    comm = Comm(1, 0, Comm.unique_id())
+    a = torch.arange(1000, dtype=torch.float64, device="cuda") * 0.5
+    b = torch.arange(77, dtype=torch.float32, device="cuda") - 30
+    ra, rb = a.clone(), b.clone()
+    comm.all_reduce(a, "sum"); comm.all_reduce(b, "max")
+    torch.cuda.synchronize()
+    assert torch.equal(a, ra) and torch.equal(b, rb)
+    with pytest.raises(ValueError):
+        comm.all_reduce(torch.zeros(4, dtype=torch.int32, device="cuda"))
+    with pytest.raises(FlaggError):
+        Comm(2, 5, Comm.unique_id())                                  # rank outside [0, nranks)
+    rng = np.random.RandomState(9)
+    X = rows_model(rng, 12, 5000, byz=2)
+    ups = dev_lists(X)
+    k0, k1 = KrumDefense({"num_malicious": 2, "multi_k": 3}), KrumDefense({"num_malicious": 2, "multi_k": 3, "process_group": comm})
+    k0.aggregate(ups, [1] * 12); k1.aggregate(ups, [1] * 12)
+    assert k0.selected_clients == k1.selected_clients and k0.client_scores == k1.client_scores
+    comm.close()
+
+
 def test_errors_surface_as_exceptions():
     from flagg import FlaggError, TRIMMED_MEAN, engine
     from src.defenses import KrumDefense, get_defense
