@@ -175,6 +175,10 @@ class Updates:
         if self._dense is not None:
             self._dense.close()
             self._dense = None
+        sub = getattr(self, "_center_sub", None)
+        if sub is not None:
+            sub.close()
+            self._center_sub = None
 
     def __del__(self):
         try:
@@ -274,11 +278,11 @@ def robust_center(u: Updates) -> torch.Tensor:
     translation invariant), so it need not be exact or agreed between ranks: with the
     parameter dimension sharded every rank centres its own columns."""
     u = u.resident()
-    idx = sorted(set(int(round(x)) for x in np.linspace(0, u.n - 1, min(u.n, CENTER_ROWS))))
-    sub = Updates([u.rows[i] for i in idx])
-    c = colwise_select(sub, MEDIAN)
-    sub.close()
-    return c
+    sub = getattr(u, "_center_sub", None)
+    if sub is None:      # the sub-view (pointer tables, tensor maps) is built once per Updates, like the main view
+        idx = sorted(set(int(round(x)) for x in np.linspace(0, u.n - 1, min(u.n, CENTER_ROWS))))
+        sub = u._center_sub = Updates([u.rows[i] for i in idx])
+    return colwise_select(sub, MEDIAN)
 
 
 def gram(u: Updates, center: Optional[torch.Tensor] = None, group=None, auto_center: bool = True) -> torch.Tensor:
