@@ -494,8 +494,19 @@ int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G
     if (pair) {
         const int nb2 = (n + T2_ROWS - 1) / T2_ROWS;
         const int tiles2 = nb2 * (nb2 + 1) / 2;
-        int64_t splits = std::max<int64_t>(1, sms / (2 * tiles2));
-        splits = std::min<int64_t>(splits, units);
+        // Split-K count: CTAs run in waves of `sms`; pick the count whose last wave is fullest
+        // (n = 1000: 20 CTAs per split, 37 splits = 740 CTAs = exactly 5 waves of 148, where
+        // 7 splits = 140 CTAs leave 8 SMs idle for the whole kernel).  Partials stay under 512 MB.
+        int64_t splits = 1;
+        {
+            const int64_t ctas = 2 * tiles2, per_split_bytes = int64_t(sizeof(double)) * ctas * (2 * TILE * TILE);
+            const int64_t smax = std::max<int64_t>(1, std::min<int64_t>({units, int64_t(96), (int64_t(512) << 20) / per_split_bytes}));
+            double best = 1e30;
+            for (int64_t sp = 1; sp <= smax; ++sp) {
+                const double cost = double((ctas * sp + sms - 1) / sms) / double(sp) + 2e-4 * double(sp);   // waves per unit of K + a little per-CTA overhead
+                if (cost < best - 1e-12) { best = cost; splits = sp; }
+            }
+        }
         const int64_t upb = (units + splits - 1) / splits;
         splits = (units + upb - 1) / upb;
         const size_t need = sizeof(double) * size_t(splits) * tiles2 * 2 * (2 * TILE * TILE);
