@@ -473,7 +473,7 @@ __global__ void gram_tc_reduce_kernel(const double* __restrict__ part, int tiles
 }  // namespace tc
 
 // Host launch; called from flagg_gram (gram.cu).  Requires 16-byte aligned segment bases.
-// Kernel choice (FLAGG_GRAM_IMPL=ss|ts|ts2 overrides): n > 256 -> CTA-pair 256x256 tiles
+// Kernel choice (FLAGG_GRAM_IMPL=ss|ts|ts2 overrides): n > 128 -> CTA-pair 256x256 tiles
 // (gram_ts2.cuh); otherwise 128x128 tiles with both operands in shared memory.
 int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st) {
     using namespace tc;
@@ -483,7 +483,7 @@ int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G
     const int sms = device_sm_count();
     const char* impl = getenv("FLAGG_GRAM_IMPL");
     const bool want_ss = impl && !strcmp(impl, "ss"), want_ts = impl && !strcmp(impl, "ts"), want_ts2 = impl && !strcmp(impl, "ts2");
-    const bool pair = want_ts2 || (!want_ss && !want_ts && n > T2_ROWS);
+    const bool pair = want_ts2 || (!want_ss && !want_ts && n > TILE);   // measured: one (diagonal) pair tile beats three 128x128 tiles from n = 129 (tools/k4_small_n.py)
     static bool attr_set = false;
     if (!attr_set) {
         FLAGG_CUDA(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));

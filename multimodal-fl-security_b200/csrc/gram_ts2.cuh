@@ -1,6 +1,6 @@
 // K4, CTA-pair variant: 256 x 256 output tiles on two SMs (tcgen05 cta_group::2), A operand from
 // tensor memory, B from shared memory.  Included by gram_tc.cu inside namespace flagg::tc after
-// gram_ts.cuh (shares ts_load, the PTX wrappers, KbIter).  Replaces krum.py:92-97 for n > 256.
+// gram_ts.cuh (shares ts_load, the PTX wrappers, KbIter).  Replaces krum.py:92-97 for n > 128.
 //
 // Why pairs.  The 128 x 128 kernels are bound by the L2 -> SM operand feed: every CTA pulls 32 KB
 // per 32-column k-block for 12 MMAs, and the pattern tops out at ~4.9 TB/s over the chip
