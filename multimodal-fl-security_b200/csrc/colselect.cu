@@ -126,6 +126,7 @@ using namespace flagg;
 extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float* out, void* stream) {
     FLAGG_REQUIRE(v && out, "flagg_colwise_select: NULL argument");
     FLAGG_REQUIRE(mode == FLAGG_MEDIAN || mode == FLAGG_TRIMMED_MEAN, "flagg_colwise_select: bad mode %d", mode);
+    const_cast<flagg_view*>(v)->last_stream = stream;
     const int n = v->dev.n;
     if (mode == FLAGG_TRIMMED_MEAN)
         FLAGG_REQUIRE(k >= 0 && n - 2 * k >= 1, "flagg_colwise_select: trimmed mean needs n-2k >= 1 (n=%d k=%d)", n, k);

@@ -64,6 +64,7 @@ struct flagg_view {
     bool dense = false;            // dev.tmaps is valid (see ViewDev::tmaps)
     int64_t total_units[flagg::NUM_GRAN] = {0, 0, 0};
     int device = 0;
+    void* last_stream = nullptr;   // stream of the latest call on this view: frees are ordered on it
     int ensure_scratch(size_t bytes);
 };
 

@@ -181,6 +181,7 @@ extern "C" {
 int flagg_gram(const flagg_view* cv, const float* center, int accumulate, double* G, void* stream) {
     FLAGG_REQUIRE(cv && G, "flagg_gram: NULL argument");
     flagg_view* v = const_cast<flagg_view*>(cv);
+    v->last_stream = stream;
     const int n = v->dev.n;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     {   // tensor-core path (gram_tc.cu) for n >= 64 on 16-byte aligned tensors; FLAGG_GRAM_IMPL=ffma|tc|ss|ts|ts2 overrides (see gram_tc_launch)

@@ -239,6 +239,7 @@ int flagg_row_reduce(const flagg_view* cv, const float* g0, int centered, double
     FLAGG_REQUIRE(!(g0_sumsq && !g0), "flagg_row_reduce: g0_sumsq requested without g0");
     FLAGG_REQUIRE(!(centered && !g0), "flagg_row_reduce: centered statistics need g0");
     flagg_view* v = const_cast<flagg_view*>(cv);
+    v->last_stream = stream;
     const int n = v->dev.n;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int64_t units = v->total_units[GRAN_2K];
@@ -279,6 +280,7 @@ int flagg_row_combine(const flagg_view* cv, int m, const int32_t* rows, const fl
                       float divisor, float* out, void* stream) {
     FLAGG_REQUIRE(cv && out, "flagg_row_combine: NULL argument");
     flagg_view* v = const_cast<flagg_view*>(cv);
+    v->last_stream = stream;
     const int n = v->dev.n;
     FLAGG_REQUIRE(m >= 1, "flagg_row_combine: m must be >= 1 (got %d)", m);
     FLAGG_REQUIRE(rows || m == n, "flagg_row_combine: rows == NULL requires m == n");

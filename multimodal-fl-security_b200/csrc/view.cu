@@ -48,13 +48,30 @@ int device_sm_count() {
 
 using namespace flagg;
 
+// Device memory of a view (tables, scratch) comes from CUDA's stream-ordered allocator with the
+// pool told to keep what is freed: a federated round creates and destroys a view per aggregate()
+// call, and cudaMalloc + cudaFree (a device-wide synchronisation) cost ~1 ms of a call whose
+// kernels take microseconds at the small shapes (tools/api_latency.py).  Frees are ordered on the
+// stream the view was last used on.
+static int pool_ready(int device) {
+    static bool done[64] = {};
+    if (device < 0 || device >= 64 || done[device]) return FLAGG_OK;
+    cudaMemPool_t pool;
+    FLAGG_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+    uint64_t keep = ~uint64_t(0);
+    FLAGG_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    done[device] = true;
+    return FLAGG_OK;
+}
+
 int flagg_view::ensure_scratch(size_t bytes) {
     if (bytes <= scratch_bytes) return FLAGG_OK;
-    if (d_scratch) FLAGG_CUDA(cudaFree(d_scratch));
+    cudaStream_t st = static_cast<cudaStream_t>(last_stream);
+    if (d_scratch) FLAGG_CUDA(cudaFreeAsync(d_scratch, st));
     d_scratch = nullptr;
     scratch_bytes = 0;
     size_t want = (bytes + 0xffff) & ~size_t(0xffff);
-    FLAGG_CUDA(cudaMalloc(&d_scratch, want));
+    FLAGG_CUDA(cudaMallocAsync(&d_scratch, want, st));
     scratch_bytes = want;
     return FLAGG_OK;
 }
@@ -137,10 +154,12 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
     const size_t b_pref = sizeof(int64_t) * (P + 1);
     const size_t b_tabs = (b_ptrs + (1 + NUM_GRAN) * b_pref + 63) & ~size_t(63);   // tensor maps need 64-byte alignment
     const size_t total = b_tabs + (v->dense ? sizeof(CUtensorMap) * P : 0);
-    e = cudaMalloc(&v->d_tables, total);
-    if (e != cudaSuccess) { delete v; set_error("cudaMalloc(view tables, %zu B): %s", total, cudaGetErrorString(e)); return FLAGG_ECUDA; }
-    char* base = static_cast<char*>(v->d_tables);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    v->last_stream = stream;
+    if (pool_ready(v->device) != FLAGG_OK) { delete v; return FLAGG_ECUDA; }
+    e = cudaMallocAsync(&v->d_tables, total, st);
+    if (e != cudaSuccess) { delete v; set_error("cudaMallocAsync(view tables, %zu B): %s", total, cudaGetErrorString(e)); return FLAGG_ECUDA; }
+    char* base = static_cast<char*>(v->d_tables);
     // Pageable sources: cudaMemcpyAsync stages them before returning, so the host
     // vectors may change afterwards; ordering w.r.t. later kernels is by stream.
     e = cudaMemcpyAsync(base, v->seg_ptrs.data(), b_ptrs, cudaMemcpyHostToDevice, st);
@@ -151,7 +170,7 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
         e = cudaMemcpyAsync(base + b_tabs, tmaps.data(), sizeof(CUtensorMap) * P, cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) {
         set_error("flagg_view_create: table upload failed: %s", cudaGetErrorString(e));
-        cudaFree(v->d_tables);
+        cudaFreeAsync(v->d_tables, st);
         delete v;
         return FLAGG_ECUDA;
     }
@@ -169,11 +188,12 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
 
 int flagg_view_destroy(flagg_view* v) {
     if (!v) return FLAGG_OK;
-    cudaError_t e1 = v->d_tables ? cudaFree(v->d_tables) : cudaSuccess;
-    cudaError_t e2 = v->d_scratch ? cudaFree(v->d_scratch) : cudaSuccess;
+    cudaStream_t st = static_cast<cudaStream_t>(v->last_stream);
+    cudaError_t e1 = v->d_tables ? cudaFreeAsync(v->d_tables, st) : cudaSuccess;
+    cudaError_t e2 = v->d_scratch ? cudaFreeAsync(v->d_scratch, st) : cudaSuccess;
     delete v;
     if (e1 != cudaSuccess || e2 != cudaSuccess) {
-        set_error("flagg_view_destroy: cudaFree failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+        set_error("flagg_view_destroy: cudaFreeAsync failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
         return FLAGG_ECUDA;
     }
     return FLAGG_OK;
