@@ -184,9 +184,9 @@ int flagg_gram(const flagg_view* cv, const float* center, int accumulate, double
     v->last_stream = stream;
     const int n = v->dev.n;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    {   // tensor-core path (gram_tc.cu) for n >= 64 on 16-byte aligned tensors; FLAGG_GRAM_IMPL=ffma|tc|ss|ts|ts2 overrides (see gram_tc_launch)
+    {   // tensor-core path (gram_tc.cu) for n >= 64 on 16-byte aligned tensors; FLAGG_GRAM_IMPL=ffma|tc|ss|ts|ts1|ts2 overrides (see gram_tc_launch)
         const char* impl = getenv("FLAGG_GRAM_IMPL");
-        const bool force_tc = impl && (!strcmp(impl, "tc") || !strcmp(impl, "ss") || !strcmp(impl, "ts") || !strcmp(impl, "ts2")), force_ffma = impl && !strcmp(impl, "ffma");
+        const bool force_tc = impl && (!strcmp(impl, "tc") || !strcmp(impl, "ss") || !strcmp(impl, "ts") || !strcmp(impl, "ts1") || !strcmp(impl, "ts2")), force_ffma = impl && !strcmp(impl, "ffma");
         if (force_tc && v->align_bytes < 16) {
             set_error("flagg_gram: FLAGG_GRAM_IMPL=tc needs 16-byte aligned tensors");
             return FLAGG_EUNSUPPORTED;

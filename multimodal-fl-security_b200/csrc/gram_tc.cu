@@ -473,8 +473,8 @@ __global__ void gram_tc_reduce_kernel(const double* __restrict__ part, int tiles
 }  // namespace tc
 
 // Host launch; called from flagg_gram (gram.cu).  Requires 16-byte aligned segment bases.
-// Kernel choice (FLAGG_GRAM_IMPL=ss|ts|ts2 overrides): n > 128 -> CTA-pair 256x256 tiles
-// (gram_ts2.cuh); otherwise 128x128 tiles with both operands in shared memory.
+// Kernel choice (FLAGG_GRAM_IMPL=ss|ts|ts1|ts2 overrides): n > 128 -> CTA-pair 256x256 tiles, n <= 128 ->
+// the same body on single CTAs (gram_ts2.cuh); ss / ts are the earlier 128x128 kernels kept for comparison.
 int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st) {
     using namespace tc;
     const int n = v->dev.n;
@@ -482,41 +482,59 @@ int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G
     FLAGG_REQUIRE(units < (int64_t(1) << 31), "flagg_gram: too many columns for the tensor-core path");
     const int sms = device_sm_count();
     const char* impl = getenv("FLAGG_GRAM_IMPL");
-    const bool want_ss = impl && !strcmp(impl, "ss"), want_ts = impl && !strcmp(impl, "ts"), want_ts2 = impl && !strcmp(impl, "ts2");
-    const bool pair = want_ts2 || (!want_ss && !want_ts && n > TILE);   // measured: one (diagonal) pair tile beats three 128x128 tiles from n = 129 (tools/k4_small_n.py)
+    auto is = [&](const char* name) { return impl && !strcmp(impl, name); };
+    const bool want_ss = is("ss"), want_ts = is("ts"), want_ts2 = is("ts2"), want_ts1 = is("ts1");
+    const bool forced = want_ss || want_ts || want_ts2 || want_ts1;
+    // measured: one (diagonal) pair tile beats three 128x128 tiles from n = 129 (tools/k4_small_n.py)
+    const bool pair = want_ts2 || (!forced && n > TILE);
+    const bool single = want_ts1 || (!forced && n <= TILE);
     static bool attr_set = false;
     if (!attr_set) {
         FLAGG_CUDA(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
         FLAGG_CUDA(cudaFuncSetAttribute(gram_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_BYTES));
         FLAGG_CUDA(cudaFuncSetAttribute(gram_ts2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
+        FLAGG_CUDA(cudaFuncSetAttribute(gram_ts1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
         attr_set = true;
     }
-    if (pair) {
-        const int nb2 = (n + T2_ROWS - 1) / T2_ROWS;
+    if (pair || single) {
+        // A-from-TMEM kernels (gram_ts2.cuh): CTA pairs on 256-row tiles, or single CTAs on 128-row tiles
+        const int ncta = pair ? 2 : 1, rows = pair ? T2_ROWS : TILE;
+        const int nb2 = (n + rows - 1) / rows;
         const int tiles2 = nb2 * (nb2 + 1) / 2;
+        const int64_t ctas = int64_t(ncta) * tiles2;
+        const int64_t per_cta_doubles = pair ? 2 * TILE * TILE : TILE * TILE;   // two N-halves per CTA
         // Split-K count: CTAs run in waves of `sms`; pick the count whose last wave is fullest
         // (n = 1000: 20 CTAs per split, 37 splits = 740 CTAs = exactly 5 waves of 148, where
         // 7 splits = 140 CTAs leave 8 SMs idle for the whole kernel).  Partials stay under 512 MB.
         int64_t splits = 1;
         {
-            const int64_t ctas = 2 * tiles2, per_split_bytes = int64_t(sizeof(double)) * ctas * (2 * TILE * TILE);
-            const int64_t smax = std::max<int64_t>(1, std::min<int64_t>({units, int64_t(96), (int64_t(512) << 20) / per_split_bytes}));
+            const int64_t per_split_bytes = int64_t(sizeof(double)) * ctas * per_cta_doubles;
+            const int64_t smax = std::max<int64_t>(1, std::min<int64_t>({units, pair ? int64_t(96) : int64_t(2 * sms), (int64_t(512) << 20) / per_split_bytes}));
+            const double per_split = pair ? 2e-4 : 2e-4 / 8;   // a little per-CTA overhead (prologue, FP64 partial tile)
             double best = 1e30;
             for (int64_t sp = 1; sp <= smax; ++sp) {
-                const double cost = double((ctas * sp + sms - 1) / sms) / double(sp) + 2e-4 * double(sp);   // waves per unit of K + a little per-CTA overhead
+                const double cost = double((ctas * sp + sms - 1) / sms) / double(sp) + per_split * double(sp);   // waves per unit of K
                 if (cost < best - 1e-12) { best = cost; splits = sp; }
             }
         }
         const int64_t upb = (units + splits - 1) / splits;
         splits = (units + upb - 1) / upb;
-        const size_t need = sizeof(double) * size_t(splits) * tiles2 * 2 * (2 * TILE * TILE);
+        const size_t need = sizeof(double) * size_t(splits) * size_t(ctas) * size_t(per_cta_doubles);
         int rc = v->ensure_scratch(need);
         if (rc != FLAGG_OK) return rc;
         double* part = static_cast<double*>(v->d_scratch);
-        dim3 grid(2 * tiles2, unsigned(splits));
-        gram_ts2_kernel<<<grid, THREADS, T2_SMEM_BYTES, st>>>(v->dev, center, nb2, units, upb, part);
-        FLAGG_CUDA(cudaGetLastError());
-        gram_ts2_reduce_kernel<<<dim3(2 * tiles2, 16), 256, 0, st>>>(part, tiles2, int(splits), nb2, n, accumulate, G);
+        const dim3 grid{unsigned(ctas), unsigned(splits), 1u};
+        // reduce: one thread per output element when there are few tiles (its loop over the splits is latency-bound)
+        const unsigned ry = ctas >= 8 ? 16u : unsigned(per_cta_doubles / 256);
+        if (pair) {
+            gram_ts2_kernel<<<grid, THREADS, T2_SMEM_BYTES, st>>>(v->dev, center, nb2, units, upb, part);
+            FLAGG_CUDA(cudaGetLastError());
+            gram_t2_reduce_kernel<true><<<dim3(unsigned(ctas), ry), 256, 0, st>>>(part, int(splits), nb2, n, accumulate, G);
+        } else {
+            gram_ts1_kernel<<<grid, THREADS, T2_SMEM_BYTES, st>>>(v->dev, center, nb2, units, upb, part);
+            FLAGG_CUDA(cudaGetLastError());
+            gram_t2_reduce_kernel<false><<<dim3(unsigned(ctas), ry), 256, 0, st>>>(part, int(splits), nb2, n, accumulate, G);
+        }
         FLAGG_CUDA(cudaGetLastError());
         return FLAGG_OK;
     }

@@ -22,7 +22,7 @@
 // starts after event e takes region (e+2)%3).  The second accumulation level (fp32, at most
 // FOLD drains = 8192 columns) lives in SHARED memory here (128 KB), the third is FP64 in global.
 //
-// Synchronisation: FULL[st] (16 producer-warp arrivals, both CTAs) and TEMPTY[region] (8 epilogue-
+// Synchronisation (a stage = 16 K positions for pairs, a 32-column k-block for single CTAs): FULL[st] (16 producer-warp arrivals, both CTAs) and TEMPTY[region] (8 epilogue-
 // warp arrivals) live in the leader CTA (rank 0) whose MMA warp issues every MMA; EMPTY[st] and
 // TFULL[region] are per CTA and signalled by multicast tcgen05.commit.
 #pragma once
@@ -31,11 +31,10 @@
 constexpr int T2_ROWS = 256;                          // pair-tile edge
 constexpr int T2_BTILE_BYTES = 64 * BK * 4;           // one B operand tile: 64 rows x 32 K = 8 KB
 constexpr int T2_SLOT_BYTES = 4 * T2_BTILE_BYTES;     // [half][hi, lo]
-constexpr int T2_SLOTS = 2;                           // k-blocks of B in flight
-constexpr int T2_NSTG = 4;                            // stages of 16 K positions (2 per k-block)
+constexpr int T2_KB_PAIR = 2, T2_KB_SINGLE = 4;       // k-blocks in flight (one 32 KB B slot + 64 TMEM columns of A each)
 constexpr int T2_ACC_BYTES = 2 * TILE * TILE * 4;     // second-level accumulator [half][col][row] fp32
-constexpr int T2_TMEM_A0 = 3 * TILE;
-constexpr int T2_BAR_OFF = T2_SLOTS * T2_SLOT_BYTES + T2_ACC_BYTES;
+constexpr int T2_BAR_OFF = T2_KB_PAIR * T2_SLOT_BYTES + T2_ACC_BYTES;   // = 4 slots + half the accumulator bytes in single-CTA form
+static_assert(T2_KB_SINGLE * T2_SLOT_BYTES + T2_ACC_BYTES / 2 == T2_BAR_OFF, "both forms share one shared-memory size");
 constexpr int T2_SMEM_BYTES = T2_BAR_OFF + 1024 + 256;
 constexpr int T2_CHUNK = KC_BLOCKS;                   // k-blocks per first-level chunk (KC = 256 columns)
 constexpr uint32_t IDESC2 = (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(128 >> 3) << 17) | (uint32_t(256 >> 4) << 24);
@@ -107,6 +106,29 @@ __device__ __forceinline__ bool elect_one() {
     asm volatile("{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\tselp.u32 %0, 1, 0, q;\n\t}" : "=r"(p));
     return p != 0;
 }
+// ---- The same body runs as a CTA pair (PAIR: cta_group::2, 256-row tiles, M = 256 x N = 128 per N-half,
+// ---- 2 stages) or as a single CTA (cta_group::1, 128-row tiles, M = 128 x N = 64 per N-half: half the
+// ---- accumulator columns, which pays for 4 stages -- a single CTA's k-block is ~1150 tensor cycles, so
+// ---- the producer -> MMA -> producer round trip needs the deeper pipeline to hide).
+__device__ __forceinline__ constexpr uint32_t idesc1(int ncols) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | (uint32_t(ncols >> 3) << 17) | (uint32_t(128 >> 4) << 24);
+}
+template <bool PAIR>
+__device__ __forceinline__ void t2_mma(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t b_hi, uint32_t accumulate, uint32_t idesc) {
+    if constexpr (PAIR) {
+        umma2_tf32_ts_lohi(d_tmem, a_tmem, b_lo, b_hi, accumulate);
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t.reg .b64 bd;\n\tsetp.ne.b32 p, %5, 0;\n\tmov.b64 bd, {%2, %3};\n\t"
+            "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], bd, %4, p;\n\t}" ::"r"(d_tmem),
+            "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
+}
+template <bool PAIR>
+__device__ __forceinline__ void t2_commit(uint32_t bar) {
+    if constexpr (PAIR) umma2_commit_both(bar); else umma_commit(bar);
+}
 __device__ __forceinline__ uint64_t pack2(float a, float b) {
     uint64_t r;
     asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
@@ -131,6 +153,8 @@ __device__ __forceinline__ void ldg_pairs44(const float* p, uint64_t (&v)[4]) {
     asm volatile("ld.global.nc.L1::no_allocate.v2.b64 {%0,%1}, [%2];" : "=l"(v[0]), "=l"(v[1]) : "l"(p));
     asm volatile("ld.global.nc.L1::no_allocate.v2.b64 {%0,%1}, [%2];" : "=l"(v[2]), "=l"(v[3]) : "l"(p + 4));
 }
+// (An L2 prefetch of the lines 6-12 k-blocks ahead was measured and rejected: it doubles the L2 request
+// count, and both forms lost 10-25 %.)
 __device__ __forceinline__ void t2_load(const KbIter& it, const TsRows& rows, bool diag, int q, T2Regs& r) {
     const int64_t col = it.c0 + it.ks + q * 8;
     const int rem = it.len - it.ks - q * 8;
@@ -179,13 +203,26 @@ __device__ __forceinline__ void t2_load(const KbIter& it, const TsRows& rows, bo
     }
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
-gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t total_units, int64_t units_per_split,
-                double* __restrict__ part) {
+template <bool PAIR>
+__device__ __forceinline__ void gram_t2_body(const ViewDev& v, const float* __restrict__ center, int nb2, int64_t total_units,
+                                             int64_t units_per_split, double* __restrict__ part) {
+    constexpr int NCTA = PAIR ? 2 : 1;            // CTAs per tile
+    constexpr int ROWS = PAIR ? T2_ROWS : TILE;   // tile edge
+    constexpr int NC = PAIR ? TILE : TILE / 2;    // accumulator columns per N-half (= TMEM region width)
+    // Pipeline stage: 16 K positions (half a k-block) in the pair form -- its two k-blocks in flight are then four
+    // stages and the MMA warp starts on a half-filled k-block -- and a whole k-block in the single-CTA form.
+    constexpr bool HALF = PAIR;
+    constexpr int NKB = PAIR ? T2_KB_PAIR : T2_KB_SINGLE;
+    constexpr int NSTG = HALF ? 2 * NKB : NKB;
+    static_assert(NSTG <= 4, "four FULL and four EMPTY barriers");
+    constexpr int TMEM_A0 = 3 * NC;               // first TMEM column of the A stages
+    static_assert(TMEM_A0 + NKB * 64 <= TMEM_COLS, "TMEM budget");
+    constexpr uint32_t HF_OFF = 2u * T2_BTILE_BYTES;                 // B rows 64-127 of this CTA (slot layout [half][hi, lo])
+    constexpr uint32_t LO_OFF = uint32_t(T2_BTILE_BYTES);            // hi -> lo operand
     extern __shared__ unsigned char smem_raw[];
     const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
     unsigned char* smem = smem_raw + (sbase - smem_u32(smem_raw));
-    float* acc = reinterpret_cast<float*>(smem + T2_SLOTS * T2_SLOT_BYTES);
+    float* acc = reinterpret_cast<float*>(smem + NKB * T2_SLOT_BYTES);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + T2_BAR_OFF);
     // bars: [0,4) FULL (leader's used), [4,8) EMPTY, [8,11) TFULL, [11,14) TEMPTY (leader's used)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
@@ -197,8 +234,8 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
     auto TEMPTY = [&](int r) { return bar0 + 8u * (11 + r); };
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const uint32_t rank = cluster_ctarank();
-    int t = int(blockIdx.x >> 1), BI = 0;
+    const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+    int t = int(PAIR ? blockIdx.x >> 1 : blockIdx.x), BI = 0;
     while (t >= nb2 - BI) { t -= nb2 - BI; ++BI; }
     const int BJ = BI + t;
     const bool diag = (BI == BJ);
@@ -206,15 +243,17 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
     const int64_t u1 = min(total_units, u0 + units_per_split);
 
     if (tid == 0) {
-        for (int s = 0; s < T2_NSTG; ++s) { mbar_init(FULL(s), 2 * PROD_WARPS); mbar_init(EMPTY(s), 1); }
-        for (int r = 0; r < 3; ++r) { mbar_init(TFULL(r), 1); mbar_init(TEMPTY(r), 2 * EPI_WARPS); }
+        for (int s = 0; s < NSTG; ++s) { mbar_init(FULL(s), NCTA * PROD_WARPS); mbar_init(EMPTY(s), 1); }
+        for (int r = 0; r < 3; ++r) { mbar_init(TFULL(r), 1); mbar_init(TEMPTY(r), NCTA * EPI_WARPS); }
         fence_barrier_init();
         *nkb_slot = int(count_kblocks(v, u0, u1));
     }
-    if (warp == MMA_WARP) tmem_alloc2(smem_u32(tmem_slot), TMEM_COLS);
+    if (warp == MMA_WARP) {
+        if constexpr (PAIR) tmem_alloc2(smem_u32(tmem_slot), TMEM_COLS); else tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
+    }
     tc_fence_before();
     __syncthreads();
-    cluster_sync_all();          // both CTAs' barriers are initialised before any remote arrive
+    if constexpr (PAIR) cluster_sync_all();   // both CTAs' barriers are initialised before any remote arrive
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const int nkb = *nkb_slot;
@@ -232,23 +271,23 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
         // B byte offset of K position 2q of row brow (see gram_ts.cuh); odd rows of an 8-row group
         // take the OTHER k-step of the stage (^ 64 bytes) so a half-warp's 8-byte stores hit 16
         // distinct bank pairs
-        const uint32_t boff = uint32_t(hf) * (2u * T2_BTILE_BYTES) + uint32_t(brow >> 3) * 1024u + uint32_t(brow & 7) * 128u +
+        const uint32_t boff = uint32_t(hf) * HF_OFF + uint32_t(brow >> 3) * 1024u + uint32_t(brow & 7) * 128u +
                               ((uint32_t((q >> 1) ^ (brow & 7)) << 4) + uint32_t(q & 1) * 8u);
         const bool odd = (r8 & 1) != 0;
         bool okA[2], okB[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            okA[h] = (BI * T2_ROWS + int(rank) * TILE + rloc + 8 * h) < v.n;
-            okB[h] = (BJ * T2_ROWS + int(rank) * TILE + rloc + 8 * h) < v.n;
+            okA[h] = (BI * ROWS + int(rank) * TILE + rloc + 8 * h) < v.n;
+            okB[h] = (BJ * ROWS + int(rank) * TILE + rloc + 8 * h) < v.n;
         }
         // padding rows of B stay zero for the whole kernel (their stores are predicated off)
-        for (int s = 0; s < T2_SLOTS; ++s)
+        for (int s = 0; s < NKB; ++s)
             for (int o = 0; o < 2; ++o)
 #pragma unroll
                 for (int h = 0; h < 2; ++h)
 #pragma unroll
                     for (int g = 0; g < 4; ++g)
-                        *reinterpret_cast<uint2*>(smem + s * T2_SLOT_BYTES + o * T2_BTILE_BYTES + ((boff + h * 1024u) ^ (uint32_t(g) << 5))) =
+                        *reinterpret_cast<uint2*>(smem + s * T2_SLOT_BYTES + o * LO_OFF + ((boff + h * 1024u) ^ (uint32_t(g) << 5))) =
                             make_uint2(0u, 0u);
         TsRows rows;
         int cur_p = -1;
@@ -256,8 +295,8 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
             uintptr_t bits = 0;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const int ra = min(BI * T2_ROWS + int(rank) * TILE + rloc + 8 * h, v.n - 1);
-                const int rb = min(BJ * T2_ROWS + int(rank) * TILE + rloc + 8 * h, v.n - 1);
+                const int ra = min(BI * ROWS + int(rank) * TILE + rloc + 8 * h, v.n - 1);
+                const int rb = min(BJ * ROWS + int(rank) * TILE + rloc + 8 * h, v.n - 1);
                 rows.a[h] = v.seg_ptrs[size_t(ra) * v.P + p];
                 rows.b[h] = v.seg_ptrs[size_t(rb) * v.P + p];
                 bits |= reinterpret_cast<uintptr_t>(rows.a[h]) | reinterpret_cast<uintptr_t>(rows.b[h]);
@@ -268,25 +307,41 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
         };
         KbIter it;
         it.init(v, u0, u1);
-        T2Regs r0, r1, r2;   // three k-blocks of loads in flight per thread
+        T2Regs r0 = {}, r1 = {}, r2 = {};   // three k-blocks of loads in flight per thread
         auto fetch = [&](T2Regs& r) {
             if (it.valid()) {
                 if (it.p != cur_p) refresh_rows(it.p);
+#ifndef T2_DBG_NOLOAD
                 t2_load(it, rows, diag, q, r);
+#endif
                 it.next(v);
             }
         };
         fetch(r0);
         fetch(r1);
         fetch(r2);
-        int stage = 0;
+        int stage = 0;                                  // stage being filled
         uint32_t phase = 1;
-        const uint32_t a_lane = tmem_base + (uint32_t(lane0) << 16) + T2_TMEM_A0;
-        const uint32_t full_leader = map_to_cta(FULL(0), 0);
+        const uint32_t a_lane = tmem_base + (uint32_t(lane0) << 16) + TMEM_A0;
+        const uint32_t full_leader = PAIR ? map_to_cta(FULL(0), 0) : FULL(0);
         constexpr uint64_t HI2 = 0xffffe000ffffe000ull;
         const bool pad_any = !(okA[0] && okA[1] && okB[0] && okB[1]);
+        // Single-CTA form: a k-block is published (FULL arrive) at the start of the NEXT emit, after the
+        // loads of the following k-block have been issued, so the TMEM-store latency overlaps them
+        // (n = 128 x 6.25M: 1.35 -> 1.04 ms).
+        int pend = -1;
+        auto publish = [&]() {
+            if (pend < 0) return;
+            tmem_wait_st();
+            tc_fence_before();
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(full_leader + 8u * uint32_t(pend));
+            pend = -1;
+        };
         auto emit = [&](T2Regs& r, auto diag_c) {
             constexpr bool DIAG = decltype(diag_c)::value;
+            publish();
             if (pad_any) {   // padding rows: x := c, so the centred value is exactly zero (A is stored unconditionally)
 #pragma unroll
                 for (int h = 0; h < 2; ++h)
@@ -318,8 +373,10 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
                         }
                     }
                 }
-                mbar_wait(EMPTY(stage), phase);
-                tc_fence_after();
+                if (HALF || sub == 0) {
+                    mbar_wait(EMPTY(stage), phase);
+                    tc_fence_after();
+                }
                 // A -> TMEM: fragment register 4 j + 2 h + e = (row h, k-step j, element e)
                 uint32_t fh[8], fl[8];
 #pragma unroll
@@ -331,10 +388,14 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
                         fl[4 * j + 2 * h] = uint32_t(al[h][j]);
                         fl[4 * j + 2 * h + 1] = uint32_t(al[h][j] >> 32);
                     }
-                tmem_st_16x256b_x2(a_lane + uint32_t(stage * 32), fh);
-                tmem_st_16x256b_x2(a_lane + uint32_t(stage * 32 + 16), fl);
+#ifndef T2_DBG_NOSTTM
+                tmem_st_16x256b_x2(a_lane + uint32_t(HALF ? stage * 32 : stage * 64 + sub * 32), fh);
+                tmem_st_16x256b_x2(a_lane + uint32_t(HALF ? stage * 32 : stage * 64 + sub * 32) + 16u, fl);
+#else
+                asm volatile("" ::"r"(fh[0] ^ fh[1] ^ fh[2] ^ fh[3] ^ fh[4] ^ fh[5] ^ fh[6] ^ fh[7] ^ fl[0] ^ fl[1] ^ fl[2] ^ fl[3] ^ fl[4] ^ fl[5] ^ fl[6] ^ fl[7]));
+#endif
                 // B -> smem: store i writes k-step j = i for even rows, j = 1 - i for odd rows
-                const uint32_t sb = sbase + uint32_t(stage >> 1) * T2_SLOT_BYTES;
+                const uint32_t sb = sbase + uint32_t(HALF ? stage >> 1 : stage) * T2_SLOT_BYTES;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
 #pragma unroll
@@ -345,18 +406,19 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
                         asm volatile(
                             "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %3, 0;\n\t"
                             "@p st.shared.b64 [%0], %1;\n\t"
-                            "@p st.shared.b64 [%0+8192], %2;\n\t}" ::"r"(addr), "l"(vh), "l"(vl), "r"(uint32_t(okB[h]))
+                            "@p st.shared.b64 [%0+%4], %2;\n\t}" ::"r"(addr), "l"(vh), "l"(vl), "r"(uint32_t(okB[h])), "n"(LO_OFF)
                             : "memory");
                     }
                 }
-                tmem_wait_st();
-                tc_fence_before();
-                fence_proxy_async();
-                __syncwarp();
-                if (lane == 0) mbar_arrive_cluster(full_leader + 8u * stage);
-                if (++stage == T2_NSTG) { stage = 0; phase ^= 1; }
+                if (HALF || sub == 1) {   // the stage is written
+                    pend = stage;
+                    if (++stage == NSTG) { stage = 0; phase ^= 1; }
+                    if constexpr (PAIR) publish();   // two k-blocks in flight only: a deferred arrive would idle the MMA warp
+                }
             }
         };
+        // (Five register sets on diagonal tiles -- the B registers are dead there -- were measured and
+        // rejected: the five-fold unrolled emit body ran 40 % slower than three sets.)
         auto run = [&](auto diag_c) {
             for (int kb = 0; kb < nkb; kb += 3) {
                 emit(r0, diag_c);
@@ -372,48 +434,75 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
             }
         };
         if (diag) run(std::true_type{}); else run(std::false_type{});
+        publish();
     } else if (warp == MMA_WARP) {
         // ================================ MMA issuer (leader CTA only) ================================
         if (rank == 0) {
             int s = 0;
             uint32_t full_phase = 0;
             const uint32_t blo0 = uint32_t(make_desc(sbase));      // low descriptor word of slot 0, half 0, hi tile, k-step 0
-            const uint32_t a_tm0 = tmem_base + T2_TMEM_A0;
+            const uint32_t a_tm0 = tmem_base + TMEM_A0;
             uint32_t tempty_uses = 0;          // bit r: parity of the next wait on TEMPTY[r]
             int reg[2] = {1, 0};               // accumulator region of half 0 / half 1
             bool fresh[2] = {true, true};      // next MMA of the half starts a chunk (overwrite)
             int ev = 0;                        // drain events committed so far
+            // single CTA, n - 128 BJ <= 64: the second N-half holds only padding rows, so its MMAs are skipped
+            // (its drain events still run; the reduce kernel never reads those columns)
+            const int nh = (!PAIR && v.n - BJ * ROWS <= TILE / 2) ? 1 : 2;
+            constexpr uint32_t idesc = idesc1(64);
             for (int kb = 0; kb < nkb; ++kb) {
+                const uint32_t d0 = tmem_base + uint32_t(reg[0] * NC), d1 = tmem_base + uint32_t(reg[1] * NC);
+                const uint32_t acc0 = fresh[0] ? 0u : 1u, acc1 = fresh[1] ? 0u : 1u;
+                // the 3 x 2 MMAs of sub-stage `sub`, k-step j (K position 32 (sub + 2 j) bytes into the 128-byte row;
+                // descriptor start address (>> 4) advances by 2 per 32-byte k-step)
+                auto issue = [&](int sub, int j, uint32_t lo0, uint32_t a_hi) {
+                    const uint32_t kofs = uint32_t(2 * sub + 4 * j);
 #pragma unroll
-                for (int sub = 0; sub < 2; ++sub) {
-                    mbar_wait_cluster(FULL(s), full_phase);
-                    tc_fence_after();
-                    {
-                        // descriptor low words: start address (>> 4) advances by 2 per 32-byte k-step
-                        const uint32_t lo0 = blo0 + uint32_t(s >> 1) * (T2_SLOT_BYTES >> 4) + uint32_t(sub) * 2u;
+                    for (int hf = 0; hf < 2; ++hf) {
+                        if (hf >= nh) continue;
+#ifdef T2_DBG_NOMMA
+                        continue;
+#endif
+                        const uint32_t d = hf ? d1 : d0;
+                        const uint32_t b_hi = lo0 + kofs + uint32_t(hf) * (HF_OFF >> 4), b_lo = b_hi + (LO_OFF >> 4);
+                        t2_mma<PAIR>(d, a_hi + 8 * j, b_hi, DESC_HI, (sub == 0 && j == 0) ? (hf ? acc1 : acc0) : 1u, idesc);
+                        t2_mma<PAIR>(d, a_hi + 8 * j, b_lo, DESC_HI, 1u, idesc);
+                        t2_mma<PAIR>(d, a_hi + 16 + 8 * j, b_hi, DESC_HI, 1u, idesc);
+                    }
+                };
+                if constexpr (HALF) {
+#pragma unroll
+                    for (int sub = 0; sub < 2; ++sub) {
+                        mbar_wait_cluster(FULL(s), full_phase);
+                        tc_fence_after();
+                        const uint32_t lo0 = blo0 + uint32_t(s >> 1) * (T2_SLOT_BYTES >> 4);
                         const uint32_t a_hi = a_tm0 + uint32_t(s * 32);
-                        const uint32_t d0 = tmem_base + uint32_t(reg[0] * TILE), d1 = tmem_base + uint32_t(reg[1] * TILE);
-                        const uint32_t acc0 = fresh[0] ? 0u : 1u, acc1 = fresh[1] ? 0u : 1u;
                         const uint32_t empty_s = EMPTY(s);
                         if (elect_one()) {
 #pragma unroll
-                            for (int j = 0; j < 2; ++j) {
-#pragma unroll
-                                for (int hf = 0; hf < 2; ++hf) {
-                                    const uint32_t d = hf ? d1 : d0;
-                                    const uint32_t b_hi = lo0 + uint32_t(4 * j + hf * (2 * T2_BTILE_BYTES >> 4)), b_lo = b_hi + (T2_BTILE_BYTES >> 4);
-                                    umma2_tf32_ts_lohi(d, a_hi + 8 * j, b_hi, DESC_HI, j == 0 ? (hf ? acc1 : acc0) : 1u);
-                                    umma2_tf32_ts_lohi(d, a_hi + 8 * j, b_lo, DESC_HI, 1u);
-                                    umma2_tf32_ts_lohi(d, a_hi + 16 + 8 * j, b_hi, DESC_HI, 1u);
-                                }
-                            }
-                            umma2_commit_both(empty_s);
+                            for (int j = 0; j < 2; ++j) issue(sub, j, lo0, a_hi);
+                            t2_commit<PAIR>(empty_s);
                         }
-                        fresh[0] = fresh[1] = false;
+                        __syncwarp();
+                        if (++s == NSTG) { s = 0; full_phase ^= 1; }
+                    }
+                } else {
+                    mbar_wait_cluster(FULL(s), full_phase);
+                    tc_fence_after();
+                    const uint32_t lo0 = blo0 + uint32_t(s) * (T2_SLOT_BYTES >> 4);
+                    const uint32_t a_hi0 = a_tm0 + uint32_t(s * 64);
+                    const uint32_t empty_s = EMPTY(s);
+                    if (elect_one()) {
+#pragma unroll
+                        for (int sub = 0; sub < 2; ++sub)
+#pragma unroll
+                            for (int j = 0; j < 2; ++j) issue(sub, j, lo0, a_hi0 + uint32_t(32 * sub));
+                        t2_commit<PAIR>(empty_s);
                     }
                     __syncwarp();
-                    if (++s == T2_NSTG) { s = 0; full_phase ^= 1; }
+                    if (++s == NSTG) { s = 0; full_phase ^= 1; }
                 }
+                fresh[0] = fresh[1] = false;
                 // chunk boundaries after k-block kb: half 1 at 4, 12, 20, ...; half 0 at 8, 16, ...; both at the end
                 const int done = kb + 1;
                 int nclose = 0;
@@ -421,7 +510,7 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
                 else if (done % (T2_CHUNK / 2) == 0) nclose = 1;
                 for (int c = 0; c < nclose; ++c) {
                     const int hf = (ev + 1) & 1, r = ev % 3;
-                    if (elect_one()) umma2_commit_both(TFULL(r));
+                    if (elect_one()) t2_commit<PAIR>(TFULL(r));
                     __syncwarp();
                     if (done < nkb) {
                         // the half continues in region (ev + 2) % 3, which event ev - 1 drained
@@ -442,20 +531,20 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(T2_EPI_REGS));
         const int row = warp * 32 + lane;
         const uint32_t lane_base = tmem_base + (uint32_t(warp * 32) << 16);
-        double* my = part + ((size_t(blockIdx.y) * (gridDim.x >> 1) + (blockIdx.x >> 1)) * 2 + rank) * (2 * TILE * TILE) + row;
-        const uint32_t tempty_leader = map_to_cta(TEMPTY(0), 0);
+        double* my = part + (size_t(blockIdx.y) * gridDim.x + blockIdx.x) * (2 * NC * TILE) + row;   // (split, tile, rank)
+        const uint32_t tempty_leader = PAIR ? map_to_cta(TEMPTY(0), 0) : TEMPTY(0);
         int cnt[2] = {0, 0};
         bool folded[2] = {false, false};
         for (int e = 0; e < n_ev; ++e) {
             const int r = e % 3, hf = (e + 1) & 1;
             mbar_wait(TFULL(r), uint32_t((e / 3) & 1));
             tc_fence_after();
-            float* a = acc + hf * (TILE * TILE) + row;
+            float* a = acc + hf * (NC * TILE) + row;
             const bool add = cnt[hf] > 0;
 #pragma unroll 1
-            for (int g = 0; g < TILE / EG; ++g) {
+            for (int g = 0; g < NC / EG; ++g) {
                 float x[EG];
-                tmem_ld16(lane_base + uint32_t(r * TILE + g * EG), x);
+                tmem_ld16(lane_base + uint32_t(r * NC + g * EG), x);
                 tmem_wait_ld();
 #pragma unroll
                 for (int i = 0; i < EG; ++i) {
@@ -468,46 +557,62 @@ gram_ts2_kernel(ViewDev v, const float* __restrict__ center, int nb2, int64_t to
             if (lane == 0) mbar_arrive_cluster(tempty_leader + 8u * r);
             ++cnt[hf];
             if (cnt[hf] == FOLD || e >= n_ev - 2) {
-                double* o = my + size_t(hf) * (TILE * TILE);
+                double* o = my + size_t(hf) * (NC * TILE);
 #pragma unroll 4
-                for (int c = 0; c < TILE; ++c) {
+                for (int c = 0; c < NC; ++c) {
+                    // later folds add in place with a fire-and-forget reduction (same thread, same address,
+                    // program order: the FP64 sum is the one a load-add-store would give, without the load latency)
                     const double x = double(a[c * TILE]);
-                    o[size_t(c) * TILE] = folded[hf] ? o[size_t(c) * TILE] + x : x;
+                    if (folded[hf]) asm volatile("red.global.add.f64 [%0], %1;" ::"l"(o + size_t(c) * TILE), "d"(x) : "memory");
+                    else o[size_t(c) * TILE] = x;
                 }
                 folded[hf] = true;
                 cnt[hf] = 0;
             }
         }
         if (n_ev == 0) {
-            for (int c = 0; c < 2 * TILE; ++c) my[size_t(c) * TILE] = 0.0;
+            for (int c = 0; c < 2 * NC; ++c) my[size_t(c) * TILE] = 0.0;
         }
     }
     tc_fence_before();
     __syncthreads();
-    cluster_sync_all();          // no CTA leaves (or frees TMEM) while its peer may still signal it
+    if constexpr (PAIR) cluster_sync_all();   // no CTA leaves (or frees TMEM) while its peer may still signal it
     if (warp == MMA_WARP) {
         tc_fence_after();
-        tmem_dealloc2(tmem_base, TMEM_COLS);
+        if constexpr (PAIR) tmem_dealloc2(tmem_base, TMEM_COLS); else tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
-// Sum the split partials in split order and scatter pair tile (BI, BJ) (and its mirror) into G.
-// Partial layout per (split, pair tile, rank): [half][col 128][row 128] doubles.
-__global__ void gram_ts2_reduce_kernel(const double* __restrict__ part, int tiles2, int splits, int nb2, int n, int accumulate,
-                                       double* __restrict__ G) {
-    int t = blockIdx.x >> 1, BI = 0;
-    const int rank = blockIdx.x & 1;
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
+gram_ts2_kernel(const __grid_constant__ ViewDev v, const float* __restrict__ center, int nb2, int64_t total_units,
+                int64_t units_per_split, double* __restrict__ part) {
+    gram_t2_body<true>(v, center, nb2, total_units, units_per_split, part);
+}
+// single-CTA form (128 x 128 tiles): the kernel for 64 <= n <= 128, where one CTA pair would leave half its rows as padding
+__global__ void __launch_bounds__(THREADS, 1)
+gram_ts1_kernel(const __grid_constant__ ViewDev v, const float* __restrict__ center, int nb, int64_t total_units,
+                int64_t units_per_split, double* __restrict__ part) {
+    gram_t2_body<false>(v, center, nb, total_units, units_per_split, part);
+}
+
+// Sum the split partials in split order and scatter tile (BI, BJ) (and its mirror) into G.
+// Partial layout per (split, tile, rank): [half][col NC][row 128] doubles.
+template <bool PAIR>
+__global__ void gram_t2_reduce_kernel(const double* __restrict__ part, int splits, int nb2, int n, int accumulate, double* __restrict__ G) {
+    constexpr int NCTA = PAIR ? 2 : 1, ROWS = PAIR ? T2_ROWS : TILE, NC = PAIR ? TILE : TILE / 2;
+    int t = int(blockIdx.x) / NCTA, BI = 0;
+    const int rank = int(blockIdx.x) % NCTA;
     while (t >= nb2 - BI) { t -= nb2 - BI; ++BI; }
     const int BJ = BI + t;
-    constexpr int PER = 2 * TILE * TILE;
+    constexpr int PER = 2 * NC * TILE;
     for (int e = blockIdx.y * blockDim.x + threadIdx.x; e < PER; e += gridDim.y * blockDim.x) {
-        const int lr = e % TILE, c = (e / TILE) % TILE, hf = e / (TILE * TILE);
-        const int i = BI * T2_ROWS + rank * TILE + lr;
-        const int j = BJ * T2_ROWS + 128 * (c >> 6) + 64 * hf + (c & 63);
+        const int lr = e % TILE, c = (e / TILE) % NC, hf = e / (NC * TILE);
+        const int i = BI * ROWS + rank * TILE + lr;
+        const int j = BJ * ROWS + (PAIR ? 128 * (c >> 6) + 64 * hf + (c & 63) : 64 * hf + c);
         if (i >= n || j >= n) continue;
         if (BI == BJ && j < i) continue;
         double s = 0.0;
-        for (int sp = 0; sp < splits; ++sp) s += part[(size_t(sp) * tiles2 + (blockIdx.x >> 1)) * (2 * PER) + size_t(rank) * PER + e];
+        for (int sp = 0; sp < splits; ++sp) s += part[(size_t(sp) * gridDim.x + blockIdx.x) * PER + e];
         if (accumulate) {
             G[size_t(i) * n + j] += s;
             if (i != j) G[size_t(j) * n + i] += s;

@@ -246,7 +246,7 @@ def test_gram_distances_scores_vs_fp64(n, d, f):
     u.close()
 
 
-@pytest.mark.parametrize("impl", ["tc", "ss", "ts", "ts2", "ffma"])
+@pytest.mark.parametrize("impl", ["tc", "ss", "ts", "ts1", "ts2", "ffma"])
 @pytest.mark.parametrize("n,seg,f", [(64, [4096], 10), (128, [32], 20), (65, [3000], 10), (130, [2048, 1], 20),
                                      (200, [780, 64, 5000], 50), (257, [33, 95, 4100], 60), (600, [5000, 77, 1300], 100),
                                      (1000, [7000, 36, 3000], 100)])
@@ -301,7 +301,7 @@ def test_gram_tc_is_default_for_large_n_and_falls_back_when_unaligned(monkeypatc
     u_al.close(); u_unal.close()
 
 
-@pytest.mark.parametrize("impl,n", [("ss", 96), ("ts", 96), ("ts2", 96), ("ts2", 300)])
+@pytest.mark.parametrize("impl,n", [("ss", 96), ("ts", 96), ("ts1", 96), ("ts1", 300), ("ts2", 96), ("ts2", 300)])
 def test_gram_tensor_core_paths_on_16_byte_aligned_views(impl, n, monkeypatch):
     """Rows that are views of one matrix with a 16-byte (not 32-byte) multiple pitch: the
     tensor-core producers must take their 128-bit load path; centred Gram against FP64."""
