@@ -21,6 +21,7 @@
 namespace flagg {
 
 int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st);  // gram_tc.cu
+int gram_small_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st);  // gram_small.cu (n <= 32)
 
 constexpr int GT = 64;          // output tile edge
 constexpr int GK = 32;          // columns per k-step (128 B of every row)
@@ -184,14 +185,24 @@ int flagg_gram(const flagg_view* cv, const float* center, int accumulate, double
     v->last_stream = stream;
     const int n = v->dev.n;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    {   // tensor-core path (gram_tc.cu) for n >= 64 on 16-byte aligned tensors; FLAGG_GRAM_IMPL=ffma|tc|ss|ts|ts1|ts2 overrides (see gram_tc_launch)
+    {   // Kernel choice (FLAGG_GRAM_IMPL=small|ffma|tc|ss|ts|ts1|ts2 overrides, see gram_tc_launch):
+        //   n <= 32            register-tile kernel (gram_small.cu), any alignment
+        //   n >= 33, aligned   tensor cores (gram_tc.cu: single CTAs up to n = 128, CTA pairs above)
+        //   otherwise          64x64 FFMA tiles (below)
         const char* impl = getenv("FLAGG_GRAM_IMPL");
-        const bool force_tc = impl && (!strcmp(impl, "tc") || !strcmp(impl, "ss") || !strcmp(impl, "ts") || !strcmp(impl, "ts1") || !strcmp(impl, "ts2")), force_ffma = impl && !strcmp(impl, "ffma");
+        auto is = [&](const char* name) { return impl && !strcmp(impl, name); };
+        const bool force_tc = is("tc") || is("ss") || is("ts") || is("ts1") || is("ts2"), force_ffma = is("ffma"), force_small = is("small");
         if (force_tc && v->align_bytes < 16) {
             set_error("flagg_gram: FLAGG_GRAM_IMPL=tc needs 16-byte aligned tensors");
             return FLAGG_EUNSUPPORTED;
         }
-        if (v->total_units[GRAN_128] > 0 && v->align_bytes >= 16 && !force_ffma && (n >= 64 || force_tc))
+        if (force_small && n > 32) {   // GS_MAX_N
+            set_error("flagg_gram: FLAGG_GRAM_IMPL=small needs n <= 32");
+            return FLAGG_EUNSUPPORTED;
+        }
+        if (v->total_units[GRAN_128] > 0 && !force_ffma && !force_tc && (n <= 32 || force_small))
+            return gram_small_launch(v, center, accumulate, G, st);
+        if (v->total_units[GRAN_128] > 0 && v->align_bytes >= 16 && !force_ffma && (n > 32 || force_tc))
             return gram_tc_launch(v, center, accumulate, G, st);
     }
     const int nb = (n + GT - 1) / GT;

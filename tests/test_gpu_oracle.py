@@ -277,6 +277,62 @@ def test_gram_paths_vs_fp64(n, seg, f, impl, monkeypatch):
     u.close()
 
 
+@pytest.mark.parametrize("impl", ["auto", "small", "ffma", "ts1"])
+@pytest.mark.parametrize("n,seg,f", [(4, [4096], 0), (8, [777, 33], 2), (9, [5000, 1, 260], 2), (10, [288, 32, 18432, 64, 401408, 128, 1280, 10], 2),
+                                     (16, [3000], 4), (17, [64, 2050], 4), (20, [130000, 36], 5), (25, [4100, 95], 6),
+                                     (32, [9000, 31], 8), (33, [4096, 100], 8), (50, [3000, 36], 12)])
+def test_gram_small_cohorts_vs_fp64(n, seg, f, impl, monkeypatch):
+    """K4 for the reference's default cohort sizes: n <= 32 runs the register-tile kernel
+    (gram_small.cu), 33 <= n < 64 the single-CTA tensor kernel; each forced kernel and the
+    dispatcher's choice against FP64 -- distances within 1e-5 relative, exact symmetry, zero
+    distance between duplicates, identical Krum selection.  Ragged segments (1, 31, 33, 95
+    columns) exercise partial 32-column groups."""
+    from flagg import engine
+    if impl == "small" and n > 32:
+        pytest.skip("gram_small serves n <= 32")
+    if impl == "auto":
+        monkeypatch.delenv("FLAGG_GRAM_IMPL", raising=False)
+    else:
+        monkeypatch.setenv("FLAGG_GRAM_IMPL", impl)
+    d = sum(seg)
+    rng = np.random.RandomState(n + d)
+    X = rows_model(rng, n, d, byz=f)
+    X[1] = X[0]
+    u = engine.Updates(dev_lists(X, seg))
+    G = engine.gram(u)
+    D, scores = engine.krum_scores(G, f)
+    D64 = oracle64.distances64(X)
+    assert D[0, 1] == 0.0 and np.all(np.diag(D) == 0) and np.array_equal(D, D.T)
+    mask = D64 > 0
+    assert np.max(np.abs(D[mask] - D64[mask]) / D64[mask]) <= 1e-5    # tolerance stated by north_star
+    if n - f - 2 >= 1:
+        s64 = oracle64.krum_scores64(D64, f)
+        np.testing.assert_allclose(scores, s64, rtol=1e-5)
+        assert int(np.argmin(scores)) == int(np.argmin(s64))
+    u.close()
+
+
+def test_gram_small_on_unaligned_views_and_accumulate(monkeypatch):
+    """The small-cohort kernel takes 4-byte aligned row views (scalar loads) and honours
+    accumulate=1 (the sharded path adds shard Grams): G(X) + G(X) == 2 G(X) bit for bit."""
+    from flagg import engine
+    monkeypatch.delenv("FLAGG_GRAM_IMPL", raising=False)
+    rng = np.random.RandomState(5)
+    n, d = 12, 5001
+    X = rows_model(rng, n, d, byz=2)
+    big = torch.from_numpy(X).cuda()
+    u = engine.Updates([[big[i]] for i in range(n)])
+    c = torch.from_numpy(np.median(X, axis=0)).cuda()
+    G = engine.gram(u, center=c).cpu().numpy()
+    Xc = X.astype(np.float64) - c.cpu().numpy().astype(np.float64)
+    G64 = Xc @ Xc.T
+    assert np.array_equal(G, G.T)
+    assert np.max(np.abs(G - G64) / np.sqrt(np.outer(np.diag(G64), np.diag(G64)))) <= 1e-6
+    G2 = engine.gram(u, center=c).cpu().numpy()
+    assert np.array_equal(G, G2)                                       # deterministic reduction order
+    u.close()
+
+
 def test_gram_tc_is_default_for_large_n_and_falls_back_when_unaligned(monkeypatch):
     """n >= 64 on 16-byte aligned tensors takes the tensor-core path; rows that are 4-byte
     aligned views take the CUDA-core path; both agree to 1e-5 on every distance."""
