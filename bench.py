@@ -178,7 +178,7 @@ def run_reference(args, rank):
 
 def extra_defenses(rank, world, dist_on, group):
     """Other defenses of the path, short runs (not the headline): trimmed mean (C2),
-    FLTrust + clipping stages (C5) and the Krum Gram (C4 shard).  GB/s = 4*n*d/t."""
+    FLTrust + clipping stages (C5) and the Krum Gram (C2 cohort, C4 shard).  GB/s = 4*n*d/t."""
     from flagg import TRIMMED_MEAN, engine
     hbm, _ = peaks()
     out = {}
@@ -208,6 +208,12 @@ def extra_defenses(rank, world, dist_on, group):
             engine.row_combine(u, None, sc, w, float(n5))         # K3
         return step
     bench("fltrust_C5_500x11.69M", n5, d5, fltrust_factory, 4.0 * d5 * (2 * n5 + 2))
+    def krum_c2_factory(u, X):
+        def step():
+            G = engine.gram(u, group=group)         # K4, small-cohort kernel (gram_small.cu)
+            engine.krum_scores(G, 5, want_D=False)                # K5
+        return step
+    bench("krum_gram_C2_20x11.69M_f5", 20, 11_689_512, krum_c2_factory, 4.0 * 20 * 11_689_512, steps=5)
     n4, d4 = 1000, 25_000_000 // 8
 
     def krum_factory(u, X):

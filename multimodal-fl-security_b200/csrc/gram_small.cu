@@ -38,6 +38,7 @@ __host__ __device__ inline GsShape gs_shape(int n) {
 }
 
 constexpr int GS_STAGES = 4;
+constexpr int GS_VEC_ITEMS = 4;            // 16-byte copies per thread per unit: ceil(32 n / threads) <= 4 for every shape
 __host__ __device__ inline int gs_rows_pad(int n) { return (n + GS_RB - 1) / GS_RB * GS_RB; }
 __host__ __device__ inline size_t gs_stage_floats(int n, int cs) { return size_t(cs) * (gs_rows_pad(n) + 1) * 128; }
 
@@ -76,6 +77,19 @@ gram_small_kernel(ViewDev v, const float* __restrict__ center, int64_t total_uni
     int lp = (u0 < u1) ? find_segment(us, v.P, u0) : 0;
     constexpr int CH = VEC ? 4 : 1;                               // floats per copy
     constexpr int CPR = 128 / CH;                                 // copies per row
+    const float* cptr[GS_VEC_ITEMS];
+    int cp_seg = -1;
+    bool c_ok[GS_VEC_ITEMS];
+    int c_row[GS_VEC_ITEMS], c_q4[GS_VEC_ITEMS];
+    uint32_t c_dst[GS_VEC_ITEMS];
+#pragma unroll
+    for (int i = 0; i < GS_VEC_ITEMS; ++i) {
+        const int item = threadIdx.x + i * nthreads;
+        c_ok[i] = VEC && item < v.n * 32;
+        c_row[i] = item / 32;
+        c_q4[i] = (item % 32) * 4;
+        c_dst[i] = uint32_t(c_row[i] * 128 + c_q4[i]) * 4u;
+    }
     auto issue = [&](int k) {                                     // stage k -> ring slot k % GS_STAGES
         if (k < iters) {
             const uint32_t sbase = smem0 + uint32_t((k % GS_STAGES) * stage_floats) * 4u;
@@ -88,11 +102,34 @@ gram_small_kernel(ViewDev v, const float* __restrict__ center, int64_t total_uni
                 const int64_t c0 = (u - us[pj]) * 128;
                 const int len = int(min((long long)128, (long long)(v.seg_start[pj + 1] - v.seg_start[pj] - c0)));
                 const uint32_t ubase = sbase + uint32_t(j * unit_floats) * 4u;
-                for (int item = threadIdx.x; item < v.n * CPR; item += nthreads) {
-                    const int q = item % CPR, rr = item / CPR;
-                    const float* rowptr = v.seg_ptrs[size_t(rr) * v.P + pj] + c0;
-                    const int nvalid = max(0, min(CH, len - q * CH));
-                    gs_cp_async<4 * CH>(ubase + uint32_t(rr * 128 + q * CH) * 4u, rowptr + (nvalid > 0 ? q * CH : 0), 4 * nvalid);
+                if constexpr (VEC) {
+                    // a thread copies the same (row, chunk) items of every unit: row pointers cached per tensor,
+                    // shared-memory offsets and chunk columns fixed for the whole kernel
+                    if (pj != cp_seg) {
+#pragma unroll
+                        for (int i = 0; i < GS_VEC_ITEMS; ++i)
+                            if (c_ok[i]) cptr[i] = v.seg_ptrs[size_t(c_row[i]) * v.P + pj] + c_q4[i];
+                        cp_seg = pj;
+                    }
+                    if (len == 128) {
+#pragma unroll
+                        for (int i = 0; i < GS_VEC_ITEMS; ++i)
+                            if (c_ok[i]) gs_cp_async<16>(ubase + c_dst[i], cptr[i] + c0, 16);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < GS_VEC_ITEMS; ++i)
+                            if (c_ok[i]) {
+                                const int nvalid = max(0, min(4, len - c_q4[i]));
+                                gs_cp_async<16>(ubase + c_dst[i], cptr[i] + c0 - (nvalid > 0 ? 0 : c_q4[i]), 4 * nvalid);
+                            }
+                    }
+                } else {
+                    for (int item = threadIdx.x; item < v.n * CPR; item += nthreads) {
+                        const int q = item % CPR, rr = item / CPR;
+                        const float* rowptr = v.seg_ptrs[size_t(rr) * v.P + pj] + c0;
+                        const int nvalid = max(0, min(CH, len - q * CH));
+                        gs_cp_async<4>(ubase + uint32_t(rr * 128 + q * CH) * 4u, rowptr + (nvalid > 0 ? q * CH : 0), 4 * nvalid);
+                    }
                 }
                 // the centre row: 4-byte copies (center + seg_start[p] is only 4-byte aligned in general); zero-filled without a centre
                 if (threadIdx.x < 128) {
@@ -212,10 +249,11 @@ int gram_small_launch(flagg_view* v, const float* center, int accumulate, double
     const GsShape sh = gs_shape(n);
     const int sms = device_sm_count();
     // CTAs: enough that a lane never accumulates more than GS_MAX_LANE_COLS columns in fp32, and a
-    // multiple of the SM count (one CTA per SM: 64 accumulators + two operand sets per thread)
+    // multiple of the SM count (one CTA per SM: 64 accumulators + two operand sets per thread; one wave
+    // when the cap allows, so the pipeline fill and the FP64 butterfly are paid once per SM)
     const int64_t max_units = std::max<int64_t>(1, int64_t(GS_MAX_LANE_COLS) * 32 * sh.cs / 128);
     int64_t ctas = (units + max_units - 1) / max_units;
-    ctas = std::max<int64_t>(ctas, std::min<int64_t>(units, 2 * int64_t(sms)));
+    ctas = std::max<int64_t>(ctas, std::min<int64_t>(units, int64_t(sms)));
     ctas = (ctas + sms - 1) / sms * sms;
     ctas = std::min<int64_t>(ctas, units);
     const int64_t upc = (units + ctas - 1) / ctas;

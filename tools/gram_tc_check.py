@@ -66,7 +66,7 @@ def tf32_peak():
 if __name__ == "__main__":
     bad = 0
     if "--only-time" in sys.argv:
-        timing(int(os.environ.get("K4_N", 1000)), int(os.environ.get("K4_D", 3_125_000)), sys.argv[-1] if sys.argv[-1] in ("tc", "ss", "ts", "ts1", "ts2") else "tc", reps=2)
+        timing(int(os.environ.get("K4_N", 1000)), int(os.environ.get("K4_D", 3_125_000)), sys.argv[-1] if sys.argv[-1] in ("tc", "ss", "ts", "ts1", "ts2", "small", "ffma") else "tc", reps=2)
         sys.exit(0)
     if "--peak" in sys.argv:
         tf32_peak()
