@@ -32,8 +32,10 @@ __host__ __device__ inline GsShape gs_shape(int n) {
     GsShape s;
     s.nblk = (n + GS_RB - 1) / GS_RB;
     s.tp = s.nblk * (s.nblk + 1) / 2;                       // 1, 3, 6, 10
-    s.cs = s.tp == 1 ? 8 : s.tp == 3 ? 4 : s.tp == 6 ? 2 : 1;
-    s.warps = s.tp * s.cs;                                  // 8, 12, 12, 10
+    // column slots: CTAs of 4-6 warps run two to an SM (independent barrier domains hide each other's
+    // stalls: a diagonal warp has 144 FMAs per unit, an off-diagonal one 256), the 10-warp shape runs alone
+    s.cs = s.tp == 1 ? 4 : s.tp == 3 ? 2 : 1;
+    s.warps = s.tp * s.cs;                                  // 4, 6, 6, 10
     return s;
 }
 
@@ -253,8 +255,9 @@ int gram_small_launch(flagg_view* v, const float* center, int accumulate, double
     // when the cap allows, so the pipeline fill and the FP64 butterfly are paid once per SM)
     const int64_t max_units = std::max<int64_t>(1, int64_t(GS_MAX_LANE_COLS) * 32 * sh.cs / 128);
     int64_t ctas = (units + max_units - 1) / max_units;
-    ctas = std::max<int64_t>(ctas, std::min<int64_t>(units, int64_t(sms)));
-    ctas = (ctas + sms - 1) / sms * sms;
+    const int per_sm = sh.warps <= 6 ? 2 : 1;
+    ctas = std::max<int64_t>(ctas, std::min<int64_t>(units, int64_t(sms) * per_sm));
+    ctas = (ctas + sms * per_sm - 1) / (sms * per_sm) * (sms * per_sm);
     ctas = std::min<int64_t>(ctas, units);
     const int64_t upc = (units + ctas - 1) / ctas;
     ctas = (units + upc - 1) / upc;
