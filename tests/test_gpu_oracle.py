@@ -330,6 +330,16 @@ def test_gram_small_on_unaligned_views_and_accumulate(monkeypatch):
     assert np.max(np.abs(G - G64) / np.sqrt(np.outer(np.diag(G64), np.diag(G64)))) <= 1e-6
     G2 = engine.gram(u, center=c).cpu().numpy()
     assert np.array_equal(G, G2)                                       # deterministic reduction order
+    from flagg._lib import check, lib
+    Gd = torch.from_numpy(G).cuda()
+    check(lib().flagg_gram(u.view(), c.data_ptr(), 1, Gd.data_ptr(), torch.cuda.current_stream().cuda_stream), "flagg_gram")
+    assert np.array_equal(Gd.cpu().numpy(), 2.0 * G)                   # accumulate=1 adds the same sums
+    monkeypatch.setenv("FLAGG_GRAM_IMPL", "small")
+    big2 = torch.from_numpy(rows_model(rng, 40, 512, byz=4)).cuda()
+    u40 = engine.Updates([[big2[i]] for i in range(40)])
+    with pytest.raises(engine.FlaggError):                             # the forced kernel refuses n > 32 loudly
+        engine.gram(u40)
+    u40.close()
     u.close()
 
 
