@@ -107,20 +107,23 @@ class Updates:
         self.on_host = not first[0].is_cuda
         self.device = first[0].device
         rows = []
+        numel, on_host, f32 = self.numel, self.on_host, torch.float32   # this loop is the fixed cost of a call at small shapes
         for i, upd in enumerate(client_updates):
             if len(upd) != self.P:
                 raise ValueError(f"client {i} has {len(upd)} tensors, expected {self.P}")
             row = []
+            push = row.append
             for p, t in enumerate(upd):
-                if int(t.numel()) != self.numel[p]:
+                if t.numel() != numel[p]:
                     raise ValueError(f"client {i} tensor {p}: {tuple(t.shape)} != {self.shapes[p]}")
-                if t.is_cuda == self.on_host:
+                if t.is_cuda == on_host:
                     raise ValueError("client updates mix host and device tensors")
+                if t.requires_grad:
+                    t = t.detach()
                 # every reference defense .float()s on flatten/stack (krum.py:57, trimmed_mean.py:79)
-                t = t.detach()
-                if t.dtype != torch.float32 or not t.is_contiguous():
-                    t = t.to(torch.float32).contiguous()
-                row.append(t)
+                if t.dtype is not f32 or not t.is_contiguous():
+                    t = t.to(f32).contiguous()
+                push(t)
             rows.append(row)
         self.rows = rows          # keeps every tensor alive while a view points at it
         self._view = None
@@ -177,8 +180,9 @@ class Updates:
             self._dense = None
         sub = getattr(self, "_center_sub", None)
         if sub is not None:
-            sub.close()
             self._center_sub = None
+            if sub is not self:
+                sub.close()
 
     def __del__(self):
         try:
@@ -281,7 +285,8 @@ def robust_center(u: Updates) -> torch.Tensor:
     sub = getattr(u, "_center_sub", None)
     if sub is None:      # the sub-view (pointer tables, tensor maps) is built once per Updates, like the main view
         idx = sorted(set(int(round(x)) for x in np.linspace(0, u.n - 1, min(u.n, CENTER_ROWS))))
-        sub = u._center_sub = Updates([u.rows[i] for i in idx])
+        # up to 31 clients every row is used: the Updates is its own sub-view (no second pointer table / view)
+        sub = u._center_sub = u if len(idx) == u.n else Updates([u.rows[i] for i in idx])
     return colwise_select(sub, MEDIAN)
 
 
