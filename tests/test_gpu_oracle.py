@@ -312,6 +312,27 @@ def test_gram_small_cohorts_vs_fp64(n, seg, f, impl, monkeypatch):
     u.close()
 
 
+@pytest.mark.parametrize("n", [1, 2, 3, 31])
+def test_gram_small_many_tiny_tensors(n, monkeypatch):
+    """Hundreds of tensors of 1..300 elements (biases, norm scales): every 128-column unit is
+    partial, stages straddle tensors, and the centre row changes alignment per tensor."""
+    from flagg import engine
+    monkeypatch.delenv("FLAGG_GRAM_IMPL", raising=False)
+    rng = np.random.RandomState(100 + n)
+    seg = [int(x) for x in rng.randint(1, 301, size=257)]
+    d = sum(seg)
+    X = rows_model(rng, n, d, byz=0)
+    u = engine.Updates(dev_lists(X, seg))
+    c = torch.from_numpy(X[0] + np.float32(1e-4)).cuda()
+    for center in (None, c):
+        G = engine.gram(u, center=center, auto_center=False).cpu().numpy()
+        Xc = X.astype(np.float64) - (0.0 if center is None else center.cpu().numpy().astype(np.float64))
+        G64 = Xc @ Xc.T
+        assert np.array_equal(G, G.T)
+        assert np.max(np.abs(G - G64) / np.sqrt(np.outer(np.diag(G64), np.diag(G64)))) <= 1e-5
+    u.close()
+
+
 def test_gram_small_on_unaligned_views_and_accumulate(monkeypatch):
     """The small-cohort kernel takes 4-byte aligned row views (scalar loads) and honours
     accumulate=1 (the sharded path adds shard Grams): G(X) + G(X) == 2 G(X) bit for bit."""
