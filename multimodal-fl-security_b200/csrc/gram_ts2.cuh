@@ -134,6 +134,11 @@ __device__ __forceinline__ uint64_t pack2(float a, float b) {
     asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
     return r;
 }
+__device__ __forceinline__ uint64_t half2x(uint64_t a) {   // (0.5 a.x, 0.5 a.y): exact
+    uint64_t r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(0x3f0000003f000000ull));
+    return r;
+}
 __device__ __forceinline__ uint64_t sub2(uint64_t a, uint64_t b) {
     uint64_t r;
     asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
@@ -364,7 +369,9 @@ __device__ __forceinline__ void gram_t2_body(const ViewDev& v, const float* __re
                         ah[h][j] = ta & HI2;
                         al[h][j] = sub2(ta, ah[h][j]);
                         if constexpr (DIAG) {
-                            bh[h][j] = ah[h][j];
+                            // diagonal tile: D' = hi (hi/2 + lo)^T, G = D' + D'^T (two products instead of three,
+                            // no lo operand in TMEM); the reduce kernel adds the transpose
+                            bh[h][j] = half2x(ah[h][j]);
                             bl[h][j] = al[h][j];
                         } else {
                             const uint64_t tb = sub2(r.b[h][g], c2);
@@ -390,7 +397,7 @@ __device__ __forceinline__ void gram_t2_body(const ViewDev& v, const float* __re
                     }
 #ifndef T2_DBG_NOSTTM
                 tmem_st_16x256b_x2(a_lane + uint32_t(HALF ? stage * 32 : stage * 64 + sub * 32), fh);
-                tmem_st_16x256b_x2(a_lane + uint32_t(HALF ? stage * 32 : stage * 64 + sub * 32) + 16u, fl);
+                if constexpr (!DIAG) tmem_st_16x256b_x2(a_lane + uint32_t(HALF ? stage * 32 : stage * 64 + sub * 32) + 16u, fl);
 #else
                 asm volatile("" ::"r"(fh[0] ^ fh[1] ^ fh[2] ^ fh[3] ^ fh[4] ^ fh[5] ^ fh[6] ^ fh[7] ^ fl[0] ^ fl[1] ^ fl[2] ^ fl[3] ^ fl[4] ^ fl[5] ^ fl[6] ^ fl[7]));
 #endif
@@ -467,7 +474,7 @@ __device__ __forceinline__ void gram_t2_body(const ViewDev& v, const float* __re
                         const uint32_t b_hi = lo0 + kofs + uint32_t(hf) * (HF_OFF >> 4), b_lo = b_hi + (LO_OFF >> 4);
                         t2_mma<PAIR>(d, a_hi + 8 * j, b_hi, DESC_HI, (sub == 0 && j == 0) ? (hf ? acc1 : acc0) : 1u, idesc);
                         t2_mma<PAIR>(d, a_hi + 8 * j, b_lo, DESC_HI, 1u, idesc);
-                        t2_mma<PAIR>(d, a_hi + 16 + 8 * j, b_hi, DESC_HI, 1u, idesc);
+                        if (!diag) t2_mma<PAIR>(d, a_hi + 16 + 8 * j, b_hi, DESC_HI, 1u, idesc);
                     }
                 };
                 if constexpr (HALF) {
@@ -612,7 +619,17 @@ __global__ void gram_t2_reduce_kernel(const double* __restrict__ part, int split
         if (i >= n || j >= n) continue;
         if (BI == BJ && j < i) continue;
         double s = 0.0;
-        for (int sp = 0; sp < splits; ++sp) s += part[(size_t(sp) * gridDim.x + blockIdx.x) * PER + e];
+        if (BI == BJ) {   // diagonal tile: the kernel left D' = hi (hi/2 + lo)^T; G = D' + D'^T
+            const int ii = i - BI * ROWS, jj = j - BJ * ROWS;
+            const int rank2 = PAIR ? jj / TILE : 0, lr2 = jj % TILE;
+            const int e2 = PAIR ? ((ii % TILE) / 64) * (NC * TILE) + (64 * (ii / TILE) + ii % 64) * TILE + lr2
+                                : (ii / 64) * (NC * TILE) + (ii % 64) * TILE + lr2;
+            const size_t b1 = size_t(blockIdx.x), b2 = size_t(blockIdx.x) - rank + rank2;
+            for (int sp = 0; sp < splits; ++sp)
+                s += part[(size_t(sp) * gridDim.x + b1) * PER + e] + part[(size_t(sp) * gridDim.x + b2) * PER + e2];
+        } else {
+            for (int sp = 0; sp < splits; ++sp) s += part[(size_t(sp) * gridDim.x + blockIdx.x) * PER + e];
+        }
         if (accumulate) {
             G[size_t(i) * n + j] += s;
             if (i != j) G[size_t(j) * n + i] += s;
