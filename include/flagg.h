@@ -55,6 +55,14 @@ typedef enum flagg_select_mode {
 
 typedef enum flagg_reduce_op { FLAGG_SUM = 0, FLAGG_MAX = 1 } flagg_reduce_op;
 
+/* Elementwise row transforms (the reference's model-poisoning attacks, src/attacks/model_poisoning.py). */
+typedef enum flagg_transform_op {
+    FLAGG_T_SCALE = 0,    /* out = x * s                 ScalingAttack :236; IPM negation (s = -1) :273 */
+    FLAGG_T_REPLACE = 1,  /* out = y + (x - y) * s       ModelReplacementAttack :74-77 (x = local, y = global) */
+    FLAGG_T_SIGN = 2,     /* out = s * sign(x)           InnerProductManipulationAttack :279-281 (s = -epsilon) */
+    FLAGG_T_AXPY = 3      /* out = x + y * s             AdaptiveKrumAttack :172-184 (x = centre, y = direction) */
+} flagg_transform_op;
+
 typedef struct flagg_view flagg_view;
 typedef struct flagg_comm flagg_comm;
 #define FLAGG_UNIQUE_ID_BYTES 128
@@ -75,6 +83,12 @@ int flagg_device_info(int* sm_count, int* cc_major, int* cc_minor);
 int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
                       const void* const* seg_ptrs, void* stream);
 int flagg_view_destroy(flagg_view* v);
+/* Round epilogue (experiments/run_experiments.py:255-259: `param.copy_(new_val)` per tensor
+ * after aggregate): out_seg_ptrs = HOST array [P] of DEVICE addresses, tensor p of every later
+ * [d] result of this view (flagg_colwise_select, flagg_row_combine*) is written to
+ * out_seg_ptrs[p] -- e.g. the global model's own parameter tensors -- instead of the flat
+ * `out` argument, which may then be NULL.  NULL clears the table. */
+int flagg_view_set_outputs(flagg_view* v, void* const* out_seg_ptrs, void* stream);
 int64_t flagg_view_cols(const flagg_view* v); /* d = sum(seg_numel) */
 int flagg_view_rows(const flagg_view* v);     /* n */
 
@@ -86,7 +100,10 @@ int flagg_view_rows(const flagg_view* v);     /* n */
  *                       (value, index) tie rule for +-0 and "any NaN -> first NaN".
  *   FLAGG_TRIMMED_MEAN  replaces torch.sort + slice [k:n-k] + mean(dim=0)
  *                       (trimmed_mean.py:82-88); requires 1 <= n-2k; NaN sorts last.
- *                       The kept values are summed in FP64 and rounded once. */
+ *                       The kept values are summed in fp32 from the middle ranks outwards
+ *                       and multiplied by fp32(1/(n-2k)) (error <= n/2 ulp of mean|kept|,
+ *                       inside the 1e-5 tolerance; Tensor.mean's own order is not
+ *                       reproducible -- DESIGN.md 3.1). */
 int flagg_colwise_select(const flagg_view* v, int mode, int k, float* out, void* stream);
 
 /* ---- K2: streaming row reductions ------------------------------------------ */
@@ -114,6 +131,20 @@ int flagg_row_reduce(const flagg_view* v, const float* g0, int centered, double*
 int flagg_row_combine(const flagg_view* v, int m, const int32_t* rows, const float* w1,
                       const float* w2, float divisor, float* out, void* stream);
 
+/* Same combination with every operand resident on the DEVICE (no host round trip between the
+ * reductions that produce the weights and this pass): d_rows [m] int32 or NULL, d_w1 / d_w2 [m]
+ * fp32 or NULL (= 1.0f), d_divisor one fp32.  With `prev` (device fp32 [d]) and `delta_sumsq`
+ * (device, one double) it also returns ||out - prev||^2 (fp32 differences and squares, FP64 sum
+ * in a fixed order): the Weiszfeld stopping rule torch.norm(new - current) at trimmed_mean.py:255. */
+int flagg_row_combine_dev(const flagg_view* v, int m, const int32_t* d_rows, const float* d_w1,
+                          const float* d_w2, const float* d_divisor, float* out, const float* prev,
+                          double* delta_sumsq, void* stream);
+
+/* Weiszfeld weights on the device (trimmed_mean.py:245-251): dist_i = max(fp32 sqrt(sumsq_i), 1e-10),
+ * w_i = 1 / dist_i, *wsum = sum_i w_i (FP64 sum rounded once).  sumsq: device FP64 [n] (the centred
+ * flagg_row_reduce output, all-reduced when sharded); w: device fp32 [n]; wsum: device fp32 [1]. */
+int flagg_weiszfeld_weights(const double* sumsq, int n, float* w, float* wsum, void* stream);
+
 /* ---- K4/K5: Krum ------------------------------------------------------------ */
 /* G (device, FP64, n*n row-major, symmetric) = (X - c)(X - c)^T where c = `center`
  * (device fp32 [d], segments concatenated; NULL = no centring).  Pairwise distances
@@ -127,8 +158,24 @@ int flagg_gram(const flagg_view* v, const float* center, int accumulate, double*
 
 /* D[i,j] = sqrt(max(0, G_ii + G_jj - 2 G_ij)) (un-squared, as krum.py:95), D_ii = 0;
  * scores[i] = sum of the (n-f-2) smallest D[i,j], j != i (krum.py:122-129).
- * D may be NULL.  All device FP64.  Requires 1 <= n-f-2 <= n-1 and n <= 4096. */
+ * D may be NULL.  All device FP64.  Requires 1 <= n-f-2 <= n-1 and n <= 4096.
+ * Non-finite entries are propagated, not clamped: a client that sent NaN / Inf gets NaN / inf
+ * distances (as torch.norm gives at krum.py:95), NaN sorts last (np.sort, krum.py:126) and stays in
+ * the sum, so that client's score is NaN / inf and np.argsort (krum.py:174) rejects it. */
 int flagg_krum_scores(const double* G, int n, int f, double* D, double* scores, void* stream);
+/* Scores from a distance matrix the caller assembled (device FP64 [n*n], D_ii = 0): the exact path
+ * for cohorts with non-finite rows, whose distances come from flagg_row_reduce(centered) instead of
+ * the Gram matrix. */
+int flagg_krum_scores_from_distances(const double* D, int n, int f, double* scores, void* stream);
+
+/* ---- row transforms: attacks on resident rows ------------------ */
+/* One client's P tensors (seg_numel: host [P]; x_ptrs / y_ptrs / out_ptrs: HOST arrays [P] of DEVICE
+ * fp32 addresses; y_ptrs may be NULL for SCALE / SIGN; out_ptrs[p] may equal x_ptrs[p]: in place on a
+ * row of a resident update matrix).  Every multiply / add / subtract is rounded to fp32 separately in
+ * the reference's order, so results are bit-identical to its CPU path. */
+int flagg_segments_transform(int P, const int64_t* seg_numel, const void* const* x_ptrs,
+                             const void* const* y_ptrs, void* const* out_ptrs, int op, float s,
+                             void* stream);
 
 /* ---- host-resident inputs (Flower path, robust_server.py:99-108) ------------ */
 /* Same contract as flagg_colwise_select, but seg_ptrs are HOST addresses (pinned
@@ -144,8 +191,12 @@ int flagg_colwise_select_host(int n, int P, const int64_t* seg_numel,
 int flagg_host_release(void);
 
 /* Copy n host rows (P segments each) into one dense device matrix dst[n, ld]
- * (ld >= d, fp32), chunked and asynchronous on `stream`.  Used to make host inputs
- * resident for the two-pass defenses (Krum, FLTrust, clipping). */
+ * (ld >= d, fp32); work after the call on `stream` sees the data.  Used to make host inputs
+ * resident for the two-pass defenses (Krum, FLTrust, clipping; robust_server.py:99-108).
+ * Pinned sources are read by the copy engine directly (one 2-D copy per tensor when the rows sit at
+ * one pitch); pageable sources (torch.tensor(ndarray), the Flower layout) are gathered by worker
+ * threads into cached pinned bounce buffers, 8 MB per H2D copy, gather and DMA overlapped.  The
+ * call returns once every source byte has been read (sources may be freed), not once it has landed. */
 int flagg_upload_rows(int n, int P, const int64_t* seg_numel,
                       const void* const* host_seg_ptrs, float* dst, int64_t ld, void* stream);
 

@@ -115,7 +115,7 @@ colselect_radix_kernel(ViewDev v, int mode, int k, float* __restrict__ out, int6
             }
             res = float(s / double(n - 2 * k));
         }
-        out[v.seg_start[p] + c] = res;
+        *out_addr(v, out, p, c) = res;
     }
 }
 
@@ -124,7 +124,7 @@ colselect_radix_kernel(ViewDev v, int mode, int k, float* __restrict__ out, int6
 using namespace flagg;
 
 extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float* out, void* stream) {
-    FLAGG_REQUIRE(v && out, "flagg_colwise_select: NULL argument");
+    FLAGG_REQUIRE(v && (out || v->dev.out_ptrs), "flagg_colwise_select: NULL argument");
     FLAGG_REQUIRE(mode == FLAGG_MEDIAN || mode == FLAGG_TRIMMED_MEAN, "flagg_colwise_select: bad mode %d", mode);
     const_cast<flagg_view*>(v)->last_stream = stream;
     const int n = v->dev.n;
@@ -134,10 +134,11 @@ extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float*
     if (units == 0) return FLAGG_OK;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int sms = device_sm_count();
+    FLAGG_REQUIRE(sms > 0, "cannot query the SM count of the current device");
     if (n == 1) {  // median / trimmed mean of one client is that client (as float)
         for (size_t p = 0; p < v->seg_numel.size(); ++p)
             if (v->seg_numel[p] > 0)
-                FLAGG_CUDA(cudaMemcpyAsync(out + v->seg_start[p], v->seg_ptrs[p], sizeof(float) * v->seg_numel[p],
+                FLAGG_CUDA(cudaMemcpyAsync(v->out_ptrs.empty() ? static_cast<void*>(out + v->seg_start[p]) : v->out_ptrs[p], v->seg_ptrs[p], sizeof(float) * v->seg_numel[p],
                                            cudaMemcpyDeviceToDevice, st));
         return FLAGG_OK;
     }

@@ -232,7 +232,7 @@ colselect_tile_kernel(ViewDev v, int mode, int k, float* __restrict__ out, int64
             }
             res = float(s / double(n - 2 * k));
         }
-        if (ok && rg == 0) out[v.seg_start[p] + c0 + c] = res;
+        if (ok && rg == 0) *out_addr(v, out, p, c0 + c) = res;
         __syncwarp();
     }
 }
@@ -258,6 +258,7 @@ int colselect_tile_launch(const flagg_view* v, int mode, int k, float* out, cuda
     const int64_t units = v->total_units[GRAN_128];
     const int64_t ntiles = units * (128 / TCOLS);
     const int sms = device_sm_count();
+    FLAGG_REQUIRE(sms > 0, "cannot query the SM count of the current device");
     const int ctas_per_sm = int(std::max<size_t>(1, std::min<size_t>(4, budget / smem)));
     const int grid = int(std::min<int64_t>((ntiles + warps - 1) / warps, int64_t(sms) * ctas_per_sm));
     colselect_tile_kernel<<<grid, MAX_WARPS * 32, smem, st>>>(v->dev, mode, k, out, units, warps, tile_floats, v->align_bytes >= 16 ? 1 : 0);

@@ -40,7 +40,17 @@ struct ViewDev {
     // CUtensorMap[P] (64 B each, device memory) when every tensor is one dense [n x len] matrix
     // with a 16-byte-multiple row pitch -- box {128 columns, n rows}; nullptr otherwise.
     const void* tmaps;
+    // Round-epilogue form (flagg_view_set_outputs): when non-NULL, kernels that produce a [d] result
+    // write tensor p of it to out_ptrs[p] (the global model's own parameter tensors) instead of
+    // out + seg_start[p] -- the inverse of seg_ptrs; replaces the per-tensor param.copy_(new_val)
+    // loop at experiments/run_experiments.py:255-259.
+    float* const* out_ptrs;
 };
+
+// Where column c of tensor p of a [d] result goes.
+__device__ __forceinline__ float* out_addr(const ViewDev& v, float* out, int p, int64_t c) {
+    return v.out_ptrs ? v.out_ptrs[p] + c : out + v.seg_start[p] + c;
+}
 
 // Work is indexed in "units": runs of UNIT_COLS[g] columns that never cross a segment
 // (tensor) boundary.  Three granularities serve the three kernel families.
@@ -58,6 +68,8 @@ struct flagg_view {
     std::vector<int64_t> unit_start[flagg::NUM_GRAN];
     std::vector<const void*> seg_ptrs;                      // host copy [n*P]
     void* d_tables = nullptr;      // one allocation holding all device tables
+    void* d_out_ptrs = nullptr;    // [P] slot inside d_tables for flagg_view_set_outputs
+    std::vector<void*> out_ptrs;   // host copy of the output table (empty = flat output)
     void* d_scratch = nullptr;     // weights / row indices for row_combine, partials
     size_t scratch_bytes = 0;
     int align_bytes = 4;           // min alignment over all segment base addresses (4/8/16)

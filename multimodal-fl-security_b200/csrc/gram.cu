@@ -132,22 +132,36 @@ __global__ void gram_reduce_kernel(const double* __restrict__ part, int tiles, i
 // ---- K5 ------------------------------------------------------------------------------
 // One CTA per client i: D_ij in shared memory, bitonic sort, sum of ranks 1..m
 // (rank 0 is the self distance 0, as np.sort(row)[1:m+1] at krum.py:126-129).
+// Non-finite values are kept, not clamped: a NaN or infinite d^2 (a client that sent NaN / Inf)
+// gives a NaN / inf distance as torch.norm does at krum.py:95, the sort puts NaN last as np.sort
+// does (krum.py:126), and the score sum keeps them -- so such a client scores NaN / inf and
+// np.argsort (krum.py:174) ranks it last instead of first.
+__device__ __forceinline__ bool krum_after(double a, double b) {   // a sorts after b; NaN after everything
+    return (a > b) || (a != a && b == b);
+}
+
+template <bool FROM_D>
 __global__ void __launch_bounds__(256)
 krum_scores_kernel(const double* __restrict__ G, int n, int npad, int m, double* __restrict__ D,
                    double* __restrict__ scores) {
     extern __shared__ double srow[];  // [npad]
     __shared__ double red[256];
     const int i = blockIdx.x, tid = threadIdx.x;
-    const double gii = G[size_t(i) * n + i];
+    const double gii = FROM_D ? 0.0 : G[size_t(i) * n + i];
     for (int j = tid; j < npad; j += blockDim.x) {
-        double dv = __longlong_as_double(0x7ff0000000000000LL);  // +inf padding
+        double dv = __longlong_as_double(0x7ff8000000000000LL);  // NaN padding: sorts last, after real infinities
         if (j < n) {
-            const double d2 = gii + G[size_t(j) * n + j] - 2.0 * G[size_t(i) * n + j];
-            dv = (j == i) ? 0.0 : sqrt(fmax(d2, 0.0));
-            if (D) D[size_t(i) * n + j] = dv;
+            if (FROM_D) {
+                dv = G[size_t(i) * n + j];
+            } else {
+                const double d2 = gii + G[size_t(j) * n + j] - 2.0 * G[size_t(i) * n + j];
+                dv = (j == i) ? 0.0 : ((d2 != d2) ? d2 : sqrt(fmax(d2, 0.0)));
+                if (D) D[size_t(i) * n + j] = dv;
+            }
         }
         srow[j] = dv;
     }
+    if (!scores) return;   // distances only (CTA-uniform)
     __syncthreads();
     for (int k = 2; k <= npad; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
@@ -156,7 +170,7 @@ krum_scores_kernel(const double* __restrict__ G, int n, int npad, int m, double*
                 if (y > x) {
                     const double a = srow[x], b = srow[y];
                     const bool up = ((x & k) == 0);
-                    if ((a > b) == up) { srow[x] = b; srow[y] = a; }
+                    if (krum_after(a, b) == up) { srow[x] = b; srow[y] = a; }
                 }
             }
             __syncthreads();
@@ -213,6 +227,7 @@ int flagg_gram(const flagg_view* cv, const float* center, int accumulate, double
         return FLAGG_OK;
     }
     const int sms = device_sm_count();
+    FLAGG_REQUIRE(sms > 0, "cannot query the SM count of the current device");
     int64_t splits = std::max<int64_t>(1, (int64_t(sms) * 4 + tiles - 1) / tiles);
     splits = std::min<int64_t>(splits, units);
     splits = std::min<int64_t>(splits, 65535);
@@ -230,16 +245,27 @@ int flagg_gram(const flagg_view* cv, const float* center, int accumulate, double
     return FLAGG_OK;
 }
 
-int flagg_krum_scores(const double* G, int n, int f, double* D, double* scores, void* stream) {
-    FLAGG_REQUIRE(G && scores, "flagg_krum_scores: NULL argument");
+static int krum_scores_launch(const double* G, int n, int f, double* D, double* scores, bool from_d, void* stream) {
     const int m = n - f - 2;
     FLAGG_REQUIRE(n >= 1 && n <= 4096, "flagg_krum_scores: n=%d unsupported (1..4096)", n);
-    FLAGG_REQUIRE(m >= 1 && m <= n - 1, "flagg_krum_scores: need 1 <= n-f-2 <= n-1 (n=%d f=%d)", n, f);
+    FLAGG_REQUIRE(!scores || (m >= 1 && m <= n - 1), "flagg_krum_scores: need 1 <= n-f-2 <= n-1 (n=%d f=%d)", n, f);
     int npad = 2;
     while (npad < n) npad <<= 1;
-    krum_scores_kernel<<<n, 256, sizeof(double) * npad, static_cast<cudaStream_t>(stream)>>>(G, n, npad, m, D, scores);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (from_d) krum_scores_kernel<true><<<n, 256, sizeof(double) * npad, st>>>(G, n, npad, m, nullptr, scores);
+    else krum_scores_kernel<false><<<n, 256, sizeof(double) * npad, st>>>(G, n, npad, m, D, scores);
     FLAGG_CUDA(cudaGetLastError());
     return FLAGG_OK;
+}
+
+int flagg_krum_scores(const double* G, int n, int f, double* D, double* scores, void* stream) {
+    FLAGG_REQUIRE(G && (scores || D), "flagg_krum_scores: NULL argument");
+    return krum_scores_launch(G, n, f, D, scores, false, stream);
+}
+
+int flagg_krum_scores_from_distances(const double* D, int n, int f, double* scores, void* stream) {
+    FLAGG_REQUIRE(D && scores, "flagg_krum_scores_from_distances: NULL argument");
+    return krum_scores_launch(D, n, f, nullptr, scores, true, stream);
 }
 
 }  // extern "C"

@@ -250,6 +250,7 @@ int gram_small_launch(flagg_view* v, const float* center, int accumulate, double
     FLAGG_REQUIRE(n >= 1 && n <= GS_MAX_N, "flagg_gram: the small-cohort kernel serves n <= %d (n=%d)", GS_MAX_N, n);
     const GsShape sh = gs_shape(n);
     const int sms = device_sm_count();
+    FLAGG_REQUIRE(sms > 0, "cannot query the SM count of the current device");
     // CTAs: enough that a lane never accumulates more than GS_MAX_LANE_COLS columns in fp32, and a
     // multiple of the SM count (one CTA per SM: 64 accumulators + two operand sets per thread; one wave
     // when the cap allows, so the pipeline fill and the FP64 butterfly are paid once per SM)

@@ -481,6 +481,7 @@ int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G
     const int64_t units = v->total_units[GRAN_128];
     FLAGG_REQUIRE(units < (int64_t(1) << 31), "flagg_gram: too many columns for the tensor-core path");
     const int sms = device_sm_count();
+    FLAGG_REQUIRE(sms > 0, "cannot query the SM count of the current device");
     const char* impl = getenv("FLAGG_GRAM_IMPL");
     auto is = [&](const char* name) { return impl && !strcmp(impl, name); };
     const bool want_ss = is("ss"), want_ts = is("ts"), want_ts2 = is("ts2"), want_ts1 = is("ts1");

@@ -160,7 +160,9 @@ constexpr int RC_UNROLL = 8;
 template <bool VEC4>
 __global__ void __launch_bounds__(RC_THREADS)
 row_combine_kernel(ViewDev v, int m, const int* __restrict__ rows, const float* __restrict__ w1,
-                   const float* __restrict__ w2, float divisor, float* __restrict__ out) {
+                   const float* __restrict__ w2, float divisor, const float* __restrict__ divisor_dev,
+                   float* __restrict__ out, const float* __restrict__ prev, double* __restrict__ part_delta) {
+    if (divisor_dev) divisor = __ldg(divisor_dev);
     const int64_t* __restrict__ ustart = v.unit_start[GRAN_1K];
     const int64_t u = blockIdx.x;
     const int p = find_segment(ustart, v.P, u);
@@ -192,9 +194,9 @@ row_combine_kernel(ViewDev v, int m, const int* __restrict__ rows, const float* 
         for (int jj = 0; jj < RC_UNROLL; ++jj) {
             const int j = j0 + jj;
             if (j < m) {
-                const float* row = v.seg_ptrs[size_t(__ldg(rows + j)) * v.P + p] + c0;
-                a1[jj] = __ldg(w1 + j);
-                a2[jj] = __ldg(w2 + j);
+                const float* row = v.seg_ptrs[size_t(rows ? __ldg(rows + j) : j) * v.P + p] + c0;
+                a1[jj] = w1 ? __ldg(w1 + j) : 1.0f;
+                a2[jj] = w2 ? __ldg(w2 + j) : 1.0f;
                 if (vec) {
                     const float4 q4 = ldg_stream4(reinterpret_cast<const float4*>(row) + t);
                     x[jj][0] = q4.x; x[jj][1] = q4.y; x[jj][2] = q4.z; x[jj][3] = q4.w;
@@ -213,17 +215,69 @@ row_combine_kernel(ViewDev v, int m, const int* __restrict__ rows, const float* 
             }
         }
     }
-    float* o = out + v.seg_start[p] + c0;
+    float r[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) r[q] = __fdiv_rn(acc[q], divisor);
+    // the epilogue form writes straight into the caller's P parameter tensors (ViewDev::out_ptrs)
+    float* o = v.out_ptrs ? v.out_ptrs[p] + c0 : out + v.seg_start[p] + c0;
     if (vec && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-        float4 r;
-        r.x = __fdiv_rn(acc[0], divisor); r.y = __fdiv_rn(acc[1], divisor);
-        r.z = __fdiv_rn(acc[2], divisor); r.w = __fdiv_rn(acc[3], divisor);
-        reinterpret_cast<float4*>(o)[t] = r;
+        reinterpret_cast<float4*>(o)[t] = make_float4(r[0], r[1], r[2], r[3]);
     } else {
 #pragma unroll
         for (int q = 0; q < 4; ++q)
-            if (col[q] >= 0) o[col[q]] = __fdiv_rn(acc[q], divisor);
+            if (col[q] >= 0) o[col[q]] = r[q];
     }
+    if (part_delta) {   // ||out - prev||^2 of this unit (Weiszfeld stopping rule, trimmed_mean.py:255)
+        const float* pv = prev + v.seg_start[p] + c0;
+        double dl = 0.0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int cc = vec ? 4 * t + q : col[q];
+            if (cc >= 0) {
+                const float df = __fsub_rn(r[q], __ldg(pv + cc));
+                dl += double(__fmul_rn(df, df));
+            }
+        }
+        dl = warp_sum(dl);
+        __shared__ double red[RC_THREADS / 32];
+        if ((t & 31) == 0) red[t >> 5] = dl;
+        __syncthreads();
+        if (t == 0) {
+            double tot = 0.0;
+#pragma unroll
+            for (int w = 0; w < RC_THREADS / 32; ++w) tot += red[w];
+            part_delta[blockIdx.x] = tot;
+        }
+    }
+}
+
+// Sum per-CTA partials in CTA order (deterministic).
+__global__ void __launch_bounds__(256) sum_partials_kernel(const double* __restrict__ part, int64_t count, double* __restrict__ out) {
+    __shared__ double red[256];
+    double s = 0.0;
+    for (int64_t i = threadIdx.x; i < count; i += 256) s += part[i];
+    red[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *out = red[0];
+}
+
+// Weiszfeld weights (trimmed_mean.py:245-251): dist_i = clamp(fp32 ||x_i - z||, 1e-10), w_i = 1/dist_i,
+// wsum = sum_i w_i.  One warp; n is a client count.
+__global__ void __launch_bounds__(32) weiszfeld_weights_kernel(const double* __restrict__ sumsq, int n, float* __restrict__ w,
+                                                               float* __restrict__ wsum) {
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += 32) {
+        const float dist = fmaxf(float(sqrt(sumsq[i])), 1e-10f);
+        const float wi = __fdiv_rn(1.0f, sumsq[i] != sumsq[i] ? __int_as_float(0x7fc00000) : dist);
+        w[i] = wi;
+        s += double(wi);
+    }
+    s = warp_sum(s);
+    if (threadIdx.x == 0) *wsum = float(s);
 }
 
 }  // namespace flagg
@@ -245,7 +299,9 @@ int flagg_row_reduce(const flagg_view* cv, const float* g0, int centered, double
     const int64_t units = v->total_units[GRAN_2K];
     const size_t smem = size_t(n) * 16 + RR_CHUNK * 4 + size_t(n) * 4;
     FLAGG_REQUIRE(smem <= 200 * 1024, "flagg_row_reduce: n=%d too large for the per-CTA accumulators", n);
-    int nblocks = int(std::min<int64_t>(std::max<int64_t>(units, 1), int64_t(device_sm_count()) * 4));
+    const int sms = device_sm_count();
+    FLAGG_REQUIRE(sms > 0, "cannot query the SM count of the current device");
+    int nblocks = int(std::min<int64_t>(std::max<int64_t>(units, 1), int64_t(sms) * 4));
     const size_t b_d = sizeof(double) * size_t(nblocks) * n;
     const size_t b_f = sizeof(float) * size_t(nblocks) * n;
     const size_t need = 2 * b_d + ((b_f + 7) & ~size_t(7)) + sizeof(double) * nblocks;
@@ -276,10 +332,39 @@ int flagg_row_reduce(const flagg_view* cv, const float* g0, int centered, double
     return FLAGG_OK;
 }
 
+static int row_combine_launch(flagg_view* v, int m, const int* d_rows, const float* d_w1, const float* d_w2, float divisor,
+                              const float* d_divisor, float* out, const float* prev, double* delta_sumsq, size_t scratch_off,
+                              cudaStream_t st) {
+    const int64_t units = v->total_units[GRAN_1K];
+    if (units == 0) {
+        if (delta_sumsq) FLAGG_CUDA(cudaMemsetAsync(delta_sumsq, 0, sizeof(double), st));
+        return FLAGG_OK;
+    }
+    FLAGG_REQUIRE(units < (int64_t(1) << 31), "flagg_row_combine: too many column units");
+    double* part = nullptr;
+    if (delta_sumsq) {
+        scratch_off = (scratch_off + 63) & ~size_t(63);
+        // ensure_scratch may move the block: callers pass offsets, never pointers into it
+        FLAGG_REQUIRE(v->scratch_bytes >= scratch_off + sizeof(double) * size_t(units), "flagg_row_combine: internal scratch sizing");
+        part = reinterpret_cast<double*>(static_cast<char*>(v->d_scratch) + scratch_off);
+    }
+    if (v->align_bytes >= 16)
+        row_combine_kernel<true><<<unsigned(units), RC_THREADS, 0, st>>>(v->dev, m, d_rows, d_w1, d_w2, divisor, d_divisor, out, prev, part);
+    else
+        row_combine_kernel<false><<<unsigned(units), RC_THREADS, 0, st>>>(v->dev, m, d_rows, d_w1, d_w2, divisor, d_divisor, out, prev, part);
+    FLAGG_CUDA(cudaGetLastError());
+    if (delta_sumsq) {
+        sum_partials_kernel<<<1, 256, 0, st>>>(part, units, delta_sumsq);
+        FLAGG_CUDA(cudaGetLastError());
+    }
+    return FLAGG_OK;
+}
+
 int flagg_row_combine(const flagg_view* cv, int m, const int32_t* rows, const float* w1, const float* w2,
                       float divisor, float* out, void* stream) {
-    FLAGG_REQUIRE(cv && out, "flagg_row_combine: NULL argument");
+    FLAGG_REQUIRE(cv, "flagg_row_combine: NULL argument");
     flagg_view* v = const_cast<flagg_view*>(cv);
+    FLAGG_REQUIRE(out || v->dev.out_ptrs, "flagg_row_combine: NULL output (and no flagg_view_set_outputs table)");
     v->last_stream = stream;
     const int n = v->dev.n;
     FLAGG_REQUIRE(m >= 1, "flagg_row_combine: m must be >= 1 (got %d)", m);
@@ -299,13 +384,28 @@ int flagg_row_combine(const flagg_view* cv, int m, const int32_t* rows, const fl
     int* d_rows = reinterpret_cast<int*>(d_w + 2 * size_t(m));
     FLAGG_CUDA(cudaMemcpyAsync(d_w, hw.data(), sizeof(float) * 2 * size_t(m), cudaMemcpyHostToDevice, st));
     FLAGG_CUDA(cudaMemcpyAsync(d_rows, hr.data(), sizeof(int32_t) * size_t(m), cudaMemcpyHostToDevice, st));
-    const int64_t units = v->total_units[GRAN_1K];
-    if (units == 0) return FLAGG_OK;
-    FLAGG_REQUIRE(units < (int64_t(1) << 31), "flagg_row_combine: too many column units");
-    if (v->align_bytes >= 16)
-        row_combine_kernel<true><<<unsigned(units), RC_THREADS, 0, st>>>(v->dev, m, d_rows, d_w, d_w + m, divisor, out);
-    else
-        row_combine_kernel<false><<<unsigned(units), RC_THREADS, 0, st>>>(v->dev, m, d_rows, d_w, d_w + m, divisor, out);
+    return row_combine_launch(v, m, d_rows, d_w, d_w + m, divisor, nullptr, out, nullptr, nullptr, 0, st);
+}
+
+int flagg_row_combine_dev(const flagg_view* cv, int m, const int32_t* d_rows, const float* d_w1, const float* d_w2,
+                          const float* d_divisor, float* out, const float* prev, double* delta_sumsq, void* stream) {
+    FLAGG_REQUIRE(cv && d_divisor, "flagg_row_combine_dev: NULL argument");
+    flagg_view* v = const_cast<flagg_view*>(cv);
+    FLAGG_REQUIRE(out || v->dev.out_ptrs, "flagg_row_combine_dev: NULL output (and no flagg_view_set_outputs table)");
+    FLAGG_REQUIRE(m >= 1 && (d_rows || m == v->dev.n), "flagg_row_combine_dev: need m >= 1, and m == n when rows == NULL");
+    FLAGG_REQUIRE(!delta_sumsq || prev, "flagg_row_combine_dev: delta_sumsq needs prev");
+    v->last_stream = stream;
+    if (delta_sumsq) {
+        int rc = v->ensure_scratch(sizeof(double) * size_t(std::max<int64_t>(v->total_units[GRAN_1K], 1)) + 64);
+        if (rc != FLAGG_OK) return rc;
+    }
+    return row_combine_launch(v, m, d_rows, d_w1, d_w2, 1.0f, d_divisor, out, prev, delta_sumsq, 0,
+                              static_cast<cudaStream_t>(stream));
+}
+
+int flagg_weiszfeld_weights(const double* sumsq, int n, float* w, float* wsum, void* stream) {
+    FLAGG_REQUIRE(sumsq && w && wsum && n >= 1, "flagg_weiszfeld_weights: bad argument");
+    weiszfeld_weights_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(sumsq, n, w, wsum);
     FLAGG_CUDA(cudaGetLastError());
     return FLAGG_OK;
 }

@@ -36,12 +36,12 @@ static PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder() {
 int device_sm_count() {
     static thread_local int cached_dev = -1, cached = 0;
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;   // callers treat 0 as an error: no silent fallback
     if (dev != cached_dev) {
-        cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
         cached_dev = dev;
     }
-    return cached > 0 ? cached : 148;
+    return cached;
 }
 
 }  // namespace flagg
@@ -153,7 +153,8 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
     const size_t b_ptrs = sizeof(void*) * size_t(n) * P;
     const size_t b_pref = sizeof(int64_t) * (P + 1);
     const size_t b_tabs = (b_ptrs + (1 + NUM_GRAN) * b_pref + 63) & ~size_t(63);   // tensor maps need 64-byte alignment
-    const size_t total = b_tabs + (v->dense ? sizeof(CUtensorMap) * P : 0);
+    const size_t b_tmaps = v->dense ? sizeof(CUtensorMap) * P : 0;
+    const size_t total = b_tabs + b_tmaps + sizeof(void*) * P;   // tail: output pointer table (flagg_view_set_outputs)
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     v->last_stream = stream;
     if (pool_ready(v->device) != FLAGG_OK) { delete v; return FLAGG_ECUDA; }
@@ -179,6 +180,8 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
     for (int g = 0; g < NUM_GRAN; ++g)
         v->dev.unit_start[g] = reinterpret_cast<const int64_t*>(base + b_ptrs + (1 + g) * b_pref);
     v->dev.tmaps = v->dense ? base + b_tabs : nullptr;
+    v->d_out_ptrs = base + b_tabs + b_tmaps;
+    v->dev.out_ptrs = nullptr;
     v->dev.n = n;
     v->dev.P = P;
     v->dev.d = v->seg_start[P];
@@ -196,6 +199,27 @@ int flagg_view_destroy(flagg_view* v) {
         set_error("flagg_view_destroy: cudaFreeAsync failed: %s", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
         return FLAGG_ECUDA;
     }
+    return FLAGG_OK;
+}
+
+int flagg_view_set_outputs(flagg_view* v, void* const* out_seg_ptrs, void* stream) {
+    FLAGG_REQUIRE(v, "flagg_view_set_outputs: NULL view");
+    v->last_stream = stream;
+    if (!out_seg_ptrs) {
+        v->dev.out_ptrs = nullptr;
+        v->out_ptrs.clear();
+        return FLAGG_OK;
+    }
+    const int P = v->dev.P;
+    for (int p = 0; p < P; ++p) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(out_seg_ptrs[p]);
+        FLAGG_REQUIRE(a != 0 || v->seg_numel[p] == 0, "flagg_view_set_outputs: NULL output tensor %d", p);
+        FLAGG_REQUIRE((a & 3) == 0, "flagg_view_set_outputs: output tensor %d not 4-byte aligned", p);
+    }
+    v->out_ptrs.assign(out_seg_ptrs, out_seg_ptrs + P);
+    FLAGG_CUDA(cudaMemcpyAsync(v->d_out_ptrs, v->out_ptrs.data(), sizeof(void*) * P, cudaMemcpyHostToDevice,
+                               static_cast<cudaStream_t>(stream)));
+    v->dev.out_ptrs = static_cast<float* const*>(v->d_out_ptrs);
     return FLAGG_OK;
 }
 

@@ -11,6 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FLAGG_LIB") or os.path.join(_HERE, "libflagg.so")   # FLAGG_LIB: tuning builds only
 
 MEDIAN, TRIMMED_MEAN = 0, 1
+T_SCALE, T_REPLACE, T_SIGN, T_AXPY = 0, 1, 2, 3
 
 
 class FlaggError(RuntimeError):
@@ -36,13 +37,18 @@ def lib():
         "flagg_device_info": (i32, [C.POINTER(i32)] * 3),
         "flagg_view_create": (i32, [C.POINTER(vp), i32, i32, C.POINTER(i64), C.POINTER(vp), vp]),
         "flagg_view_destroy": (i32, [vp]),
+        "flagg_view_set_outputs": (i32, [vp, C.POINTER(vp), vp]),
         "flagg_view_cols": (i64, [vp]),
         "flagg_view_rows": (i32, [vp]),
         "flagg_colwise_select": (i32, [vp, i32, i32, vp, vp]),
         "flagg_row_reduce": (i32, [vp, vp, i32, vp, vp, vp, vp, vp]),
         "flagg_row_combine": (i32, [vp, i32, C.POINTER(C.c_int32), C.POINTER(f32), C.POINTER(f32), f32, vp, vp]),
+        "flagg_row_combine_dev": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, vp, vp]),
+        "flagg_weiszfeld_weights": (i32, [vp, i32, vp, vp, vp]),
         "flagg_gram": (i32, [vp, vp, i32, vp, vp]),
         "flagg_krum_scores": (i32, [vp, i32, i32, vp, vp, vp]),
+        "flagg_krum_scores_from_distances": (i32, [vp, i32, i32, vp, vp]),
+        "flagg_segments_transform": (i32, [i32, C.POINTER(i64), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), i32, f32, vp]),
         "flagg_colwise_select_host": (i32, [i32, i32, C.POINTER(i64), C.POINTER(vp), i32, i32, vp, i64]),
         "flagg_upload_rows": (i32, [i32, i32, C.POINTER(i64), C.POINTER(vp), vp, i64, vp]),
         "flagg_host_release": (i32, []),
@@ -62,6 +68,7 @@ def lib():
 
 
 EXPORTS = ["flagg_version", "flagg_last_error", "flagg_device_info", "flagg_view_create", "flagg_view_destroy",
+           "flagg_view_set_outputs", "flagg_row_combine_dev", "flagg_weiszfeld_weights", "flagg_krum_scores_from_distances", "flagg_segments_transform",
            "flagg_view_cols", "flagg_view_rows", "flagg_colwise_select", "flagg_row_reduce", "flagg_row_combine",
            "flagg_gram", "flagg_krum_scores", "flagg_colwise_select_host", "flagg_upload_rows", "flagg_host_release", "flagg_comm_unique_id",
            "flagg_comm_create", "flagg_comm_destroy", "flagg_comm_size", "flagg_comm_rank", "flagg_allreduce_f64",

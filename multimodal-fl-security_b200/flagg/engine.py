@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import FlaggError, MEDIAN, TRIMMED_MEAN, check, lib
+from ._lib import FlaggError, MEDIAN, TRIMMED_MEAN, T_AXPY, T_REPLACE, T_SCALE, T_SIGN, check, lib  # noqa: F401
 
 
 def _require_cuda() -> None:
@@ -75,6 +75,16 @@ class Comm:
             self.close()
         except Exception:
             pass
+
+
+def group_rank_world(group):
+    """(rank, world) of a flagg ``Comm`` or a torch.distributed group; (0, 1) for None."""
+    if group is None:
+        return 0, 1
+    if isinstance(group, Comm):
+        return group.rank, group.nranks
+    import torch.distributed as dist
+    return dist.get_rank(group), dist.get_world_size(group)
 
 
 def all_reduce(t: torch.Tensor, group, op: str = "sum") -> torch.Tensor:
@@ -171,6 +181,34 @@ class Updates:
             self._view = h
         return self._view
 
+    # -- round epilogue: results written straight into the caller's parameter tensors ------------
+    def check_outputs(self, outputs) -> list:
+        """Validate ``outputs`` (e.g. ``list(global_model.parameters())``) as the destination of a
+        [d] result of these updates: P contiguous fp32 device tensors of the inputs' sizes."""
+        outs = [o.data if isinstance(o, torch.nn.Parameter) else o for o in outputs]
+        if self.on_host:
+            raise ValueError("'output_params' needs device-resident client updates")
+        if len(outs) != self.P:
+            raise ValueError(f"'output_params' holds {len(outs)} tensors, the updates {self.P}")
+        for p, o in enumerate(outs):
+            if not (o.is_cuda and o.device == self.device and o.dtype == torch.float32 and o.is_contiguous()
+                    and o.numel() == self.numel[p]):
+                raise ValueError(f"'output_params'[{p}] must be a contiguous fp32 tensor of {self.numel[p]} elements on {self.device}")
+        return outs
+
+    def _bind(self, outs) -> None:
+        arr = (C.c_void_p * self.P)(*[o.data_ptr() for o in outs]) if outs is not None else None
+        check(lib().flagg_view_set_outputs(self.view(), arr, _stream()), "flagg_view_set_outputs")
+
+    def scatter(self, flat: torch.Tensor, outs) -> None:
+        """flat [d] -> the P output tensors (one launch; used where the producing kernel could not
+        write them itself)."""
+        off, xs = 0, []
+        for p in range(self.P):
+            xs.append(flat[off:off + self.numel[p]])
+            off += self.numel[p]
+        segments_transform(T_SCALE, 1.0, xs, None, outs)
+
     def close(self) -> None:
         if self._view is not None:
             lib().flagg_view_destroy(self._view)
@@ -181,7 +219,7 @@ class Updates:
         sub = getattr(self, "_center_sub", None)
         if sub is not None:
             self._center_sub = None
-            if sub is not self:
+            if sub is not True:
                 sub.close()
 
     def __del__(self):
@@ -208,10 +246,21 @@ class Updates:
 # ---------------------------------------------------------------------------------------
 # kernels
 # ---------------------------------------------------------------------------------------
-def colwise_select(u: Updates, mode: int, k: int = 0) -> torch.Tensor:
+def colwise_select(u: Updates, mode: int, k: int = 0, outputs=None) -> Optional[torch.Tensor]:
     """K1.  Returns the flat fp32 result [d] on the inputs' device (host inputs are
-    streamed through the GPU by flagg_colwise_select_host and come back on the host)."""
+    streamed through the GPU by flagg_colwise_select_host and come back on the host).
+    With ``outputs`` (P device tensors, see Updates.check_outputs) the kernel writes them directly
+    and None is returned."""
     _require_cuda()
+    if outputs is not None:
+        outs = u.check_outputs(outputs)
+        with torch.cuda.device(u.device):
+            u._bind(outs)
+            try:
+                check(lib().flagg_colwise_select(u.view(), mode, k, None, _stream()), "flagg_colwise_select")
+            finally:
+                u._bind(None)
+        return None
     if u.on_host:
         out = torch.empty(u.d, dtype=torch.float32)
         seg, ptrs = u._ptr_tables()
@@ -251,8 +300,10 @@ def row_stats(u: Updates, g0_flat: Optional[torch.Tensor] = None, group=None, ce
                     linf=linf.cpu().numpy())
 
 
-def row_combine(u: Updates, rows, w1, w2, divisor: float) -> torch.Tensor:
-    """K3.  Flat fp32 [d] = (sum_j w2_j*(w1_j*x_rows[j])) / divisor, reference order."""
+def row_combine(u: Updates, rows, w1, w2, divisor: float, outputs=None) -> Optional[torch.Tensor]:
+    """K3.  Flat fp32 [d] = (sum_j w2_j*(w1_j*x_rows[j])) / divisor, reference order.
+    With ``outputs`` the kernel writes the P tensors directly and None is returned."""
+    outs = u.check_outputs(outputs) if outputs is not None else None
     u = u.resident()
     m = len(rows) if rows is not None else u.n
     def arr(x, ct):
@@ -266,10 +317,17 @@ def row_combine(u: Updates, rows, w1, w2, divisor: float) -> torch.Tensor:
     a1 = arr(w1, C.c_float)
     a2 = arr(w2, C.c_float)
     with torch.cuda.device(u.device):
-        out = torch.empty(u.d, dtype=torch.float32, device=u.device)
-        check(lib().flagg_row_combine(u.view(), m, r[0] if r else None, a1[0] if a1 else None,
-                                      a2[0] if a2 else None, float(np.float32(divisor)), out.data_ptr(), _stream()),
-              "flagg_row_combine")
+        out = torch.empty(u.d, dtype=torch.float32, device=u.device) if outs is None else None
+        if outs is not None:
+            u._bind(outs)
+        try:
+            check(lib().flagg_row_combine(u.view(), m, r[0] if r else None, a1[0] if a1 else None,
+                                          a2[0] if a2 else None, float(np.float32(divisor)),
+                                          out.data_ptr() if out is not None else None, _stream()),
+                  "flagg_row_combine")
+        finally:
+            if outs is not None:
+                u._bind(None)
     return out
 
 
@@ -285,9 +343,11 @@ def robust_center(u: Updates) -> torch.Tensor:
     sub = getattr(u, "_center_sub", None)
     if sub is None:      # the sub-view (pointer tables, tensor maps) is built once per Updates, like the main view
         idx = sorted(set(int(round(x)) for x in np.linspace(0, u.n - 1, min(u.n, CENTER_ROWS))))
-        # up to 31 clients every row is used: the Updates is its own sub-view (no second pointer table / view)
-        sub = u._center_sub = u if len(idx) == u.n else Updates([u.rows[i] for i in idx])
-    return colwise_select(sub, MEDIAN)
+        # up to 31 clients every row is used: the Updates is its own sub-view (no second pointer table / view).
+        # Marked with True, not with `u` itself: a self-reference would leave the object (its view, the caller's
+        # tensors and a dense device copy of host inputs) to the cyclic GC instead of the refcount.
+        sub = u._center_sub = True if len(idx) == u.n else Updates([u.rows[i] for i in idx])
+    return colwise_select(u if sub is True else sub, MEDIAN)
 
 
 def gram(u: Updates, center: Optional[torch.Tensor] = None, group=None, auto_center: bool = True) -> torch.Tensor:
@@ -310,15 +370,138 @@ def gram(u: Updates, center: Optional[torch.Tensor] = None, group=None, auto_cen
     return G
 
 
-def krum_scores(G: torch.Tensor, f: int, want_D: bool = True):
-    """K5.  (D [n,n] float64 ndarray or None, scores [n] float64 ndarray)."""
+def krum_scores(G: torch.Tensor, f: int, want_D: bool = True, want_scores: bool = True):
+    """K5.  (D [n,n] float64 ndarray or None, scores [n] float64 ndarray or None)."""
     n = G.shape[0]
     with torch.cuda.device(G.device):
-        scores = torch.empty(n, dtype=torch.float64, device=G.device)
+        scores = torch.empty(n, dtype=torch.float64, device=G.device) if want_scores else None
         D = torch.empty((n, n), dtype=torch.float64, device=G.device) if want_D else None
-        check(lib().flagg_krum_scores(G.data_ptr(), n, f, D.data_ptr() if want_D else None, scores.data_ptr(),
-                                      _stream()), "flagg_krum_scores")
-        return (D.cpu().numpy() if want_D else None), scores.cpu().numpy()
+        check(lib().flagg_krum_scores(G.data_ptr(), n, f, D.data_ptr() if want_D else None,
+                                      scores.data_ptr() if want_scores else None, _stream()), "flagg_krum_scores")
+        return (D.cpu().numpy() if want_D else None), (scores.cpu().numpy() if want_scores else None)
+
+
+def krum_distances_scores(u: Updates, f: int, group=None, want_D: bool = True):
+    """Krum's distance matrix and scores (krum.py:86-131): K4 Gram (+ all-reduce when sharded) and
+    K5.  A cohort with a non-finite row (a client that sent NaN / Inf) takes the exact path
+    below, so that client is ranked last as in the reference instead of poisoning the centre."""
+    u = u.resident()
+    G = gram(u, group=group)
+    D, scores = krum_scores(G, f, want_D)
+    if np.all(np.isfinite(scores)):
+        return D, scores
+    return _krum_nonfinite(u, f, group)
+
+
+def _krum_nonfinite(u: Updates, f: int, group):
+    """Rare path: some row holds NaN / Inf (every score of the Gram path is then non-finite for
+    that row, and all of them if it sat among the centre rows).  The reference's distances
+    (torch.norm(f_i - f_j), krum.py:95) are NaN / inf for pairs with such a row and ordinary
+    numbers for the rest: finite rows go through the Gram of their own sub-view, each non-finite
+    row b gets ||x_i - x_b||^2 for all i from one centred K2 pass (fp32 differences, so IEEE
+    inf / NaN arithmetic decides inf versus NaN exactly as torch.norm does), K5 ranks the assembled
+    matrix with NaN last (np.sort, krum.py:126).  Decisions use all-reduced statistics, so every
+    rank of a sharded group takes the same branch."""
+    n = u.n
+    ss = row_stats(u, group=group)["sumsq"]
+    bad = [i for i in range(n) if not np.isfinite(ss[i])]
+    good = [i for i in range(n) if np.isfinite(ss[i])]
+    D = np.zeros((n, n), dtype=np.float64)
+    if len(good) >= 2:
+        sub = Updates([u.rows[i] for i in good])
+        try:
+            Dg, _ = krum_scores(gram(sub, group=group), 0, want_D=True, want_scores=False)
+        finally:
+            sub.close()
+        D[np.ix_(good, good)] = Dg
+    with np.errstate(all="ignore"):
+        for b in bad:
+            xb = torch.cat([t.reshape(-1) for t in u.rows[b]])
+            col = np.sqrt(row_stats(u, xb, group=group, centered=True)["sumsq"])
+            D[b, :] = col
+            D[:, b] = col
+    np.fill_diagonal(D, 0.0)
+    with torch.cuda.device(u.device):
+        Dd = torch.from_numpy(D).to(u.device)
+        scores = torch.empty(n, dtype=torch.float64, device=u.device)
+        check(lib().flagg_krum_scores_from_distances(Dd.data_ptr(), n, f, scores.data_ptr(), _stream()),
+              "flagg_krum_scores_from_distances")
+        return D, scores.cpu().numpy()
+
+
+def weiszfeld(u: Updates, max_iters: int, tolerance: float, group=None):
+    """Geometric median by Weiszfeld iterations (trimmed_mean.py:240-262), host out of the loop:
+    K1 median start, then per iteration K2 (centred: ||x_i - z||^2, all-reduced when sharded), the
+    weights 1/max(dist, 1e-10) and their sum formed on the device, K3 with device-resident weights
+    whose epilogue also returns ||z_new - z||^2 (all-reduced when sharded, so every rank stops at
+    the same iteration); one 8-byte read-back per iteration decides convergence.
+    Returns (flat fp32 [d] on the device, num_iters)."""
+    u = u.resident()
+    n = u.n
+    L = lib()
+    with torch.cuda.device(u.device):
+        cur = colwise_select(u, MEDIAN)
+        new = torch.empty_like(cur)
+        ss = torch.empty(n, dtype=torch.float64, device=u.device)
+        w = torch.empty(n + 1, dtype=torch.float32, device=u.device)     # weights, then their sum
+        delta = torch.empty(1, dtype=torch.float64, device=u.device)
+        tol32 = np.float32(tolerance)
+        num_iters = max_iters
+        for it in range(max_iters):
+            st = _stream()
+            check(L.flagg_row_reduce(u.view(), cur.data_ptr(), 1, ss.data_ptr(), None, None, None, st), "flagg_row_reduce")
+            if group is not None:
+                all_reduce(ss, group, "sum")
+            check(L.flagg_weiszfeld_weights(ss.data_ptr(), n, w.data_ptr(), w.data_ptr() + 4 * n, st), "flagg_weiszfeld_weights")
+            check(L.flagg_row_combine_dev(u.view(), n, None, w.data_ptr(), None, w.data_ptr() + 4 * n, new.data_ptr(),
+                                          cur.data_ptr(), delta.data_ptr(), st), "flagg_row_combine_dev")
+            if group is not None:
+                all_reduce(delta, group, "sum")
+            cur, new = new, cur
+            with np.errstate(all="ignore"):
+                change = np.float32(np.sqrt(delta.cpu().numpy()[0]))
+            if change < tol32:                                            # trimmed_mean.py:258-260
+                num_iters = it + 1
+                break
+        return cur, num_iters
+
+
+def segments_transform(op: int, s: float, x: Sequence[torch.Tensor], y: Optional[Sequence[torch.Tensor]] = None,
+                       out: Optional[Sequence[torch.Tensor]] = None) -> List[torch.Tensor]:
+    """Elementwise transform of one client's P tensors (flagg_segments_transform): the reference's
+    model-poisoning attacks (model_poisoning.py:71-78, 236, 271-283, 172-184) in its own fp32
+    operation order.  ``out=None`` allocates fresh tensors; ``out=x`` transforms the rows of a
+    resident update matrix in place.  Host tensors are moved to the GPU and the result back."""
+    _require_cuda()
+    on_host = not x[0].is_cuda
+    dev = torch.device("cuda", torch.cuda.current_device()) if on_host else x[0].device
+
+    def prep(ts):
+        return [t.detach().to(device=dev, dtype=torch.float32).contiguous() for t in ts]
+    xs = prep(x)
+    ys = prep(y) if y is not None else None
+    if ys is not None and [t.numel() for t in ys] != [t.numel() for t in xs]:
+        raise ValueError("transform operands differ in shape")
+    if out is None:
+        outs = [torch.empty_like(t) for t in xs]
+    else:
+        outs = list(out)
+        for t, o in zip(xs, outs):
+            if not (o.is_cuda and o.dtype == torch.float32 and o.is_contiguous() and o.numel() == t.numel()):
+                raise ValueError("in-place transforms need contiguous fp32 device tensors of the operands' sizes")
+    P = len(xs)
+    seg = (C.c_int64 * P)(*[int(t.numel()) for t in xs])
+    xp = (C.c_void_p * P)(*[t.data_ptr() for t in xs])
+    yp = (C.c_void_p * P)(*[t.data_ptr() for t in ys]) if ys is not None else None
+    op_ = (C.c_void_p * P)(*[t.data_ptr() for t in outs])
+    with torch.cuda.device(dev):
+        check(lib().flagg_segments_transform(P, seg, xp, yp, op_, int(op), float(np.float32(s)), _stream()),
+              "flagg_segments_transform")
+    if out is None:
+        outs = [o.reshape(t.shape) for o, t in zip(outs, x)]
+        if on_host:
+            outs = [o.cpu() for o in outs]
+    return outs
 
 
 def device_info() -> dict:

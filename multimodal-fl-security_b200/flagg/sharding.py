@@ -42,12 +42,7 @@ def shard_update_lists(client_updates: Sequence[Sequence[torch.Tensor]], rank: i
             if b > a:
                 row.append(t.reshape(-1)[a - off:b - off])
             off += m
+        if not row:      # empty shard (lo == hi): one zero-length tensor, so the rank still joins the collectives with zeros
+            row.append(upd[0].reshape(-1)[:0])
         out.append(row)
     return out, (lo, hi)
-
-
-def allreduce_partials(partials: torch.Tensor, group=None, op="sum") -> torch.Tensor:
-    """In-place all-reduce of a rank's partial Gram matrix / partial row sums."""
-    import torch.distributed as dist
-    dist.all_reduce(partials, op=dist.ReduceOp.SUM if op == "sum" else dist.ReduceOp.MAX, group=group)
-    return partials

@@ -63,8 +63,14 @@ class DPSGDDefense(BaseDefense):
         n = u.n
         norms32 = _l2_norms32(engine.row_stats(u, group=self._group))
         flat = self._weighted_mean(u, list(range(n)), num_examples, scale=self._scales(norms32))
-        aggregated = u.split(flat, to_host=u.on_host, dtypes=_out_dtypes(u))
-        noisy = self.add_noise(aggregated, n)
+        aggregated = self._emit(u, flat, _out_dtypes(u))
+        if flat is None:      # epilogue form: the noise of :112-117 lands in the model tensors too (same RNG calls)
+            noise_std = self.clip_norm * self.noise_multiplier / n
+            for p in aggregated:
+                p.add_(torch.randn_like(p) * noise_std)
+            noisy = aggregated
+        else:
+            noisy = self.add_noise(aggregated, n)
         self.rounds_completed += 1
         self._update_privacy_spent(n)
         return noisy
@@ -127,7 +133,7 @@ class GradientClippingDefense(BaseDefense):
         self.original_norms = list(norms)
         self.clipped_count = sum(1 for v in norms if v > self.clip_norm)
         flat = self._weighted_mean(u, list(range(u.n)), num_examples, scale=[self._scale(v) for v in norms])
-        return u.split(flat, to_host=u.on_host, dtypes=_out_dtypes(u))
+        return self._emit(u, flat, _out_dtypes(u))
 
     def get_metrics(self) -> Dict[str, Any]:
         return {'defense_type': 'gradient_clipping', 'clip_norm': self.clip_norm, 'clip_type': self.clip_type,
@@ -154,7 +160,7 @@ class NormBoundingDefense(BaseDefense):
         if not keep:                                          # :319-322 all rejected -> use all
             keep = list(range(u.n))
         flat = self._weighted_mean(u, keep, num_examples)
-        return u.split(flat, to_host=u.on_host, dtypes=_out_dtypes(u))
+        return self._emit(u, flat, _out_dtypes(u))
 
     def detect_malicious(self, client_updates, num_examples) -> List[int]:
         return self.rejected_clients

@@ -16,6 +16,7 @@ import torch.optim as optim
 from torch.utils.data import DataLoader, Dataset, Subset
 
 from flagg import engine
+from flagg.sharding import shard_bounds
 from .base_defense import BaseDefense
 
 
@@ -81,35 +82,51 @@ class FLTrustDefense(BaseDefense):
     def _trust_from_stats(st):
         """fp32 arithmetic of fltrust.py:174-186 and :208-214 on the K2 reductions."""
         f32 = np.float32
-        sn = f32(np.sqrt(st['g0_sumsq']))
-        trust, scale = [], []
         with np.errstate(all='ignore'):
-            for ss, dot in zip(st['sumsq'], st['dot']):
-                cn = f32(np.sqrt(ss))
-                if cn < 1e-10 or sn < 1e-10:
-                    trust.append(0.0)
-                else:
-                    trust.append(max(0.0, float(f32(dot) / f32(cn * sn))))
-                scale.append(f32(1.0) if cn < 1e-10 else f32(sn / cn))
-        return trust, scale
+            sn = f32(np.sqrt(st['g0_sumsq']))
+            cn = np.sqrt(np.asarray(st['sumsq'], dtype=np.float64)).astype(f32)
+            q = np.asarray(st['dot'], dtype=np.float64).astype(f32) / (cn * sn)          # fp32 / fp32
+            tiny = cn < 1e-10
+            # Python's max(0.0, q) keeps 0.0 unless q > 0.0 (so NaN -> 0.0), fltrust.py:186
+            trust = np.where(~tiny & (sn >= 1e-10) & (q > 0), q, f32(0.0)).astype(np.float64)
+            scale = np.where(tiny, f32(1.0), sn / cn).astype(f32)
+        return trust.tolist(), list(scale)
 
     def aggregate(self, client_updates, num_examples, global_params: Optional[List[torch.Tensor]] = None):
         if global_params is None:
             raise ValueError("global_params must be provided for FLTrust")     # fltrust.py:235-238
         server_gradient = self._compute_server_gradient(global_params)
         u = engine.Updates(client_updates)
-        st = engine.row_stats(u, self._flatten(server_gradient), group=self._group)
+        g0 = self._flatten(server_gradient)
+        sharded = self._group is not None and g0.numel() != u.d
+        if sharded:
+            # parameter-sharded call: the clients' lists hold this rank's columns only (flagg.sharding),
+            # g0 comes from the whole model -- cut it to the same column range
+            rank, world = engine.group_rank_world(self._group)
+            lo, hi = shard_bounds(int(g0.numel()), world)[rank]
+            if hi - lo != u.d:
+                raise ValueError(f"sharded FLTrust: this rank's updates hold {u.d} columns, its shard of g0 is [{lo}, {hi})")
+            g0 = g0[lo:hi]
+        st = engine.row_stats(u, g0, group=self._group)
         self.trust_scores, scale = self._trust_from_stats(st)
         total_trust = sum(self.trust_scores)
         if total_trust < 1e-10:                                                 # :258-260
+            if self._outputs is not None:
+                u.scatter(g0.to(u.device), u.check_outputs(self._outputs))
+                return list(self._outputs)
+            if sharded:
+                return u.split(g0.to(u.device), to_host=u.on_host)
             return server_gradient
         # Zero-trust rows contribute exactly +-0 to the running sum (which starts at +0 and
         # can never be -0), so they are skipped unless the row holds Inf/NaN (0*Inf = NaN).
         rows = [i for i in range(u.n) if self.trust_scores[i] != 0.0 or not np.isfinite(st['sumsq'][i])]
         flat = engine.row_combine(u, rows, [scale[i] for i in rows],
-                                  [np.float32(self.trust_scores[i]) for i in rows], np.float32(total_trust))
+                                  [np.float32(self.trust_scores[i]) for i in rows], np.float32(total_trust),
+                                  outputs=self._outputs)
         dt = [d if d.is_floating_point else torch.float32 for d in u.in_dtypes]
-        return u.split(flat, to_host=u.on_host, dtypes=dt)
+        out = self._emit(u, flat, dt)
+        u.close()
+        return out
 
     def detect_malicious(self, client_updates, num_examples, threshold: float = 0.1) -> List[int]:
         if not self.trust_scores:

@@ -28,23 +28,18 @@ class KrumDefense(BaseDefense):
         return torch.cat([t.flatten().float() for t in update])
 
     def _distances_and_scores(self, u: engine.Updates, f: int):
-        G = engine.gram(u, group=self._group)
-        return engine.krum_scores(G, f, want_D=True)
+        return engine.krum_distances_scores(u, f, group=self._group, want_D=False)
 
     def _compute_distances(self, client_updates) -> np.ndarray:
         """Pairwise L2 distance matrix, float64 [n, n] (krum.py:73-99)."""
         u = engine.Updates(client_updates)
-        G = engine.gram(u, group=self._group)
         n = u.n
-        D, _ = engine.krum_scores(G, max(0, n - 3), want_D=True) if n >= 3 else (self._tiny_D(G), None)
+        if n >= 3:      # scores with one neighbour come for free and route non-finite rows to the exact path
+            D, _ = engine.krum_distances_scores(u, n - 3, group=self._group, want_D=True)
+        else:
+            D, _ = engine.krum_scores(engine.gram(u, group=self._group), 0, want_D=True, want_scores=False)
+        u.close()
         return D
-
-    @staticmethod
-    def _tiny_D(G):
-        g = G.cpu().numpy()
-        d2 = np.maximum(np.diag(g)[:, None] + np.diag(g)[None, :] - 2 * g, 0.0)
-        np.fill_diagonal(d2, 0.0)
-        return np.sqrt(d2)
 
     def aggregate(self, client_updates, num_examples):
         n = len(client_updates)
@@ -61,11 +56,17 @@ class KrumDefense(BaseDefense):
         self.selected_clients = sorted_indices[:self.multi_k].tolist()
         self.rejected_clients = sorted_indices[self.multi_k:].tolist()
         if self.multi_k == 1:
-            return client_updates[self.selected_clients[0]]  # the client's own list object (krum.py:178-181)
+            sel = client_updates[self.selected_clients[0]]   # the client's own list object (krum.py:178-181)
+            if self._outputs is not None:                    # epilogue form: the selected row lands in the model
+                engine.segments_transform(engine.T_SCALE, 1.0, sel, None, u.check_outputs(self._outputs))
+            u.close()
+            return sel
         # krum.py:187-190: sum(selected, in score order) / multi_k
-        flat = engine.row_combine(u, self.selected_clients, None, None, np.float32(self.multi_k))
+        flat = engine.row_combine(u, self.selected_clients, None, None, np.float32(self.multi_k), outputs=self._outputs)
         dt = [d if d.is_floating_point else torch.float32 for d in u.in_dtypes]
-        return u.split(flat, to_host=u.on_host, dtypes=dt)
+        out = self._emit(u, flat, dt)
+        u.close()      # drops the device copy of host inputs now, not at the next GC pass
+        return out
 
     def detect_malicious(self, client_updates, num_examples) -> List[int]:
         if not self.client_scores:

@@ -14,9 +14,6 @@ from flagg import engine, MEDIAN, TRIMMED_MEAN
 from .base_defense import BaseDefense
 
 
-def _f32_lists(u: engine.Updates, flat: torch.Tensor):
-    return u.split(flat, to_host=u.on_host)        # .float() outputs, trimmed_mean.py:79,160
-
 
 class TrimmedMeanDefense(BaseDefense):
     def __init__(self, defense_config: Dict[str, Any]):
@@ -30,11 +27,12 @@ class TrimmedMeanDefense(BaseDefense):
         if n - 2 * self.num_trimmed_per_end < 1:                        # :69-72
             return self._coordinate_wise_median(client_updates)
         u = engine.Updates(client_updates)
-        return _f32_lists(u, engine.colwise_select(u, TRIMMED_MEAN, self.num_trimmed_per_end))
+        # .float() outputs (trimmed_mean.py:79,160)
+        return self._emit(u, engine.colwise_select(u, TRIMMED_MEAN, self.num_trimmed_per_end, outputs=self._outputs))
 
     def _coordinate_wise_median(self, client_updates):
         u = engine.Updates(client_updates)
-        return _f32_lists(u, engine.colwise_select(u, MEDIAN))
+        return self._emit(u, engine.colwise_select(u, MEDIAN, outputs=self._outputs))
 
     def get_metrics(self) -> Dict[str, Any]:
         return {'defense_type': 'trimmed_mean', 'trim_ratio': self.trim_ratio,
@@ -50,7 +48,7 @@ class MedianDefense(BaseDefense):
 
     def aggregate(self, client_updates, num_examples):
         u = engine.Updates(client_updates)
-        return _f32_lists(u, engine.colwise_select(u, MEDIAN))
+        return self._emit(u, engine.colwise_select(u, MEDIAN, outputs=self._outputs))
 
     def get_metrics(self) -> Dict[str, Any]:
         return {'defense_type': 'median'}
@@ -70,25 +68,17 @@ class GeometricMedianDefense(BaseDefense):
         self.num_iters = 0
 
     def aggregate(self, client_updates, num_examples):
-        u = engine.Updates(client_updates).resident()
-        n = u.n
-        current = engine.colwise_select(u, MEDIAN)                       # :240
-        for iteration in range(self.max_iters):
-            # ||u_i - x|| for every client in one pass (K2, centred statistics), :245
-            st = engine.row_stats(u, current, group=self._group, centered=True)
-            dist = torch.from_numpy(np.sqrt(st['sumsq']).astype(np.float32))
-            dist = torch.clamp(dist, min=1e-10)                          # :248
-            w = (1.0 / dist)                                             # :251
-            wsum = w.sum()
-            new = engine.row_combine(u, list(range(n)), w.numpy(), None, float(wsum))
-            change = torch.norm(new - current)
-            current = new
-            if change < self.tolerance:                                  # :258-260
-                self.num_iters = iteration + 1
-                break
-        else:
-            self.num_iters = self.max_iters
-        return u.split(current, to_host=client_updates[0][0].is_cuda is False)
+        u0 = engine.Updates(client_updates)
+        # the whole loop runs on the device (engine.weiszfeld): distances, weights, combine and the
+        # stopping norm; with 'process_group' the distances and the change are whole-vector values
+        # on every rank, so all ranks stop at the same iteration (trimmed_mean.py:254-260)
+        current, self.num_iters = engine.weiszfeld(u0, self.max_iters, self.tolerance, group=self._group)
+        if self._outputs is not None:
+            u0.scatter(current, u0.check_outputs(self._outputs))
+            current = None
+        out = self._emit(u0, current)
+        u0.close()
+        return out
 
     def get_metrics(self) -> Dict[str, Any]:
         return {'defense_type': 'geometric_median', 'max_iters': self.max_iters, 'num_iters': self.num_iters}

@@ -199,3 +199,31 @@ def geometric_median(X: torch.Tensor, max_iters: int = 100, tolerance: float = 1
             iters = it + 1
             break
     return dict(out=cur, num_iters=iters)
+
+
+# ----------------------------------------------------------------------------
+# Model-poisoning attacks  (/root/reference/src/attacks/model_poisoning.py)
+# ----------------------------------------------------------------------------
+def attack_model_replacement(local: torch.Tensor, glob: torch.Tensor, num_clients: int, scale_factor: float = 10.0,
+                             num_malicious: int = 1, boost_factor=None) -> torch.Tensor:
+    """model_poisoning.py:63-78 -- old + (new - old) * scale, scale a Python float."""
+    scale = boost_factor if boost_factor is not None else (num_clients / num_malicious) * scale_factor
+    delta = local - glob
+    return glob + delta * scale
+
+
+def attack_scaling(local: torch.Tensor, scale: float = 100.0) -> torch.Tensor:
+    return local * scale                                 # :236
+
+
+def attack_ipm(local: torch.Tensor, epsilon: float = 0.1, benign_mean=None) -> torch.Tensor:
+    if benign_mean is None:
+        return -local                                    # :271-273
+    return -epsilon * torch.sign(benign_mean)            # :279-281
+
+
+def attack_adaptive_krum(benign: torch.Tensor, direction: torch.Tensor, perturbation_scale: float = 0.1):
+    """:125-138 (centre = Python sum() of the benign rows / count) and :172-184 with a
+    target_direction.  Returns (poisoned, centre)."""
+    center = _left_to_right(benign[i] for i in range(benign.shape[0])) / benign.shape[0]
+    return center + direction * perturbation_scale, center

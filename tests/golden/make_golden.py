@@ -21,6 +21,7 @@ import numpy as np
 import torch
 
 REF = "/root/reference/src/defenses"
+REF_ATTACKS = "/root/reference/src/attacks"
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
@@ -31,6 +32,20 @@ def load_reference():
     sys.modules["ref_defenses"] = mod
     spec.loader.exec_module(mod)
     return mod
+
+
+def load_reference_attacks():
+    """model_poisoning.py alone (the package __init__ pulls in the dataset attacks)."""
+    import types
+    pkg = types.ModuleType("ref_attacks")
+    pkg.__path__ = [REF_ATTACKS]
+    sys.modules["ref_attacks"] = pkg
+    for name in ("base_attack", "model_poisoning"):
+        spec = importlib.util.spec_from_file_location(f"ref_attacks.{name}", os.path.join(REF_ATTACKS, f"{name}.py"))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[f"ref_attacks.{name}"] = mod
+        spec.loader.exec_module(mod)
+    return sys.modules["ref_attacks.model_poisoning"]
 
 
 def make_rows(rng, n, d, n_byz=0, kind="replace", theta_sigma=0.05, delta_sigma=1e-3):
@@ -200,6 +215,64 @@ def main():
     df = ref.GeometricMedianDefense({"max_iters": 50})
     res = df.aggregate(to_lists(X, seg), ones(n))
     put("geomed", {"max_iters": 50}, X, seg, out=flat(res), num_iters=df.num_iters)
+
+    # ======== round 2 additions (appended: the cases above keep their random streams) ========
+    # ---------------- Krum with non-finite clients (NaN / Inf rows are ranked last, krum.py:95,126,174) --------
+    import warnings as _w
+    U32 = np.uint32
+    for name, n, f, mk, d, seg, spec in [
+            ("krum_nan_n9", 9, 2, 3, 400, [300, 100], {4: "nan"}),
+            ("krum_inf_n9", 9, 2, 3, 400, [400], {2: "+inf@7", 6: "-inf@9"}),
+            ("krum_infpair_n12", 12, 3, 4, 500, [256, 244], {1: "+inf@5", 8: "+inf@5", 10: "nan"}),
+            ("krum_nan_n40", 40, 5, 10, 300, [300], {0: "nan", 17: "+inf@3"}),     # row 0 is always a centre row
+            ("krum_nan_n70", 70, 10, 35, 260, [260], {33: "nan"})]:
+        X = make_rows(rng, n, d, n_byz=2, kind="replace")
+        for r, what in spec.items():
+            if what == "nan":
+                X.view(U32)[r, 11] = 0x7FC00000
+            else:
+                X[r, int(what.split("@")[1])] = np.inf if what[0] == "+" else -np.inf
+        df = ref.KrumDefense({"num_malicious": f, "multi_k": mk})
+        with _w.catch_warnings(), np.errstate(all="ignore"):
+            _w.simplefilter("ignore")
+            res = df.aggregate(to_lists(X, seg), ones(n))
+            D = df._compute_distances(to_lists(X, seg))
+        put(name, {"num_malicious": f, "multi_k": mk}, X, seg, out=flat(res), selected=df.selected_clients,
+            rejected=df.rejected_clients, scores=np.array(df.client_scores, dtype=np.float64), D=D)
+
+    # ---------------- geometric median, several tensors, more iterations ----------------
+    n, d, seg = 15, 1000, [512, 100, 388]
+    X = make_rows(rng, n, d, n_byz=3, kind="replace")
+    df = ref.GeometricMedianDefense({"max_iters": 100, "tolerance": 1e-6})
+    res = df.aggregate(to_lists(X, seg), ones(n))
+    put("geomed_p3", {"max_iters": 100, "tolerance": 1e-6}, X, seg, out=flat(res), num_iters=df.num_iters)
+
+    # ---------------- model-poisoning attacks (src/attacks/model_poisoning.py) ----------------
+    att = load_reference_attacks()
+    n, d, seg = 6, 900, [400, 37, 463]
+    X = make_rows(rng, n, d)
+    X[0, :6] = [0.0, -0.0, np.inf, -np.inf, 1e-40, -3e38]
+    X.view(U32)[0, 6] = 0x7FC00000
+    glob = rng.normal(0, 0.05, d).astype(np.float32)
+    direction = rng.normal(0, 1.0, d).astype(np.float32)
+    G = to_lists(glob[None, :], seg)[0]
+    L = to_lists(X, seg)
+    with _w.catch_warnings(), np.errstate(all="ignore"):
+        _w.simplefilter("ignore")
+        put("attack_replace", {"scale_factor": 10.0, "num_malicious": 2}, X, seg, glob=glob, num_clients=20,
+            out=flat(att.ModelReplacementAttack({"scale_factor": 10.0, "num_malicious": 2}).poison_update(L[0], G, 20)))
+        put("attack_replace_boost", {"boost_factor": 3.7}, X, seg, glob=glob, num_clients=20,
+            out=flat(att.ModelReplacementAttack({"boost_factor": 3.7}).poison_update(L[0], G, 20)))
+        put("attack_scaling", {"scale": 100.0}, X, seg, glob=glob,
+            out=flat(att.ScalingAttack({"scale": 100.0}).poison_update(L[0], G, 20)))
+        put("attack_ipm_negate", {"epsilon": 0.1}, X, seg, glob=glob,
+            out=flat(att.InnerProductManipulationAttack({"epsilon": 0.1}).poison_update(L[0], G, 20)))
+        put("attack_ipm_sign", {"epsilon": 0.1}, X, seg, glob=glob,
+            out=flat(att.InnerProductManipulationAttack({"epsilon": 0.1}).poison_update(L[1], G, 20, benign_mean=L[0])))
+        ak = att.AdaptiveKrumAttack({"perturbation_scale": 0.05, "target_direction": to_lists(direction[None, :], seg)[0]})
+        res = ak.poison_update(L[1], G, 20, benign_updates=L[1:])
+        put("attack_adaptive_krum", {"perturbation_scale": 0.05}, X, seg, glob=glob, direction=direction,
+            out=flat(res), center=flat(ak.estimated_benign_center))
 
     np.savez_compressed(os.path.join(HERE, "golden.npz"), **arrays)
     with open(os.path.join(HERE, "golden.json"), "w") as fh:

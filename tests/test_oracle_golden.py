@@ -53,16 +53,17 @@ def test_trim_count_double_rounding():
 def test_krum(golden, name):
     c = golden.case(name)
     r = ref_port.krum(T(c["X"]), c["cfg"]["num_malicious"], c["cfg"]["multi_k"])
-    assert np.array_equal(r["D"], c["D"])
-    assert np.array_equal(np.array(r["scores"]), c["scores"])
+    assert np.array_equal(r["D"], c["D"], equal_nan=True)       # NaN / inf rows: the krum_nan_* / krum_inf* fixtures
+    assert np.array_equal(np.array(r["scores"]), c["scores"], equal_nan=True)
     assert r["selected"] == c["selected"].tolist()
     assert r["rejected"] == c["rejected"].tolist()
     assert np.array_equal(bits(r["out"].numpy()), bits(c["out"]))
     # FP64 truth: the reference's fp32 norms are accurate at this d
-    D64 = oracle64.distances64(c["X"])
-    assert np.allclose(D64, c["D"], rtol=2e-6, atol=0)
-    s64 = oracle64.krum_scores64(D64, c["cfg"]["num_malicious"])
-    assert np.allclose(s64, c["scores"], rtol=2e-6)
+    with np.errstate(all="ignore"):
+        D64 = oracle64.distances64(c["X"])
+        assert np.allclose(D64, c["D"], rtol=2e-6, atol=0, equal_nan=True)
+        s64 = oracle64.krum_scores64(D64, c["cfg"]["num_malicious"])
+        assert np.allclose(s64, c["scores"], rtol=2e-6, equal_nan=True)
     # Multi-Krum mean == strict left-to-right fp32 sum in score order
     if c["cfg"]["multi_k"] > 1:
         seq = oracle64.combine_seq32(c["X"], None, None, c["cfg"]["multi_k"], rows=c["selected"].tolist())
@@ -121,11 +122,33 @@ def test_norm_bounding(golden, name):
     assert np.array_equal(bits(r["out"].numpy()), bits(c["out"]))
 
 
-def test_geometric_median(golden):
-    c = golden.case("geomed")
-    r = ref_port.geometric_median(T(c["X"]), c["cfg"]["max_iters"])
+@pytest.mark.parametrize("name", golden_names("geomed"))
+def test_geometric_median(golden, name):
+    c = golden.case(name)
+    r = ref_port.geometric_median(T(c["X"]), c["cfg"]["max_iters"], c["cfg"].get("tolerance", 1e-5))
     assert r["num_iters"] == int(c["num_iters"])
     assert np.array_equal(bits(r["out"].numpy()), bits(c["out"]))
+
+
+def test_attacks(golden):
+    """The reference's model-poisoning attacks (src/attacks/model_poisoning.py) restated: bit-exact
+    against fixtures produced by its own classes, incl. +-0 / Inf / NaN / denormal elements."""
+    c = golden.case("attack_replace")
+    X, g = T(c["X"]), T(c["glob"])
+    with np.errstate(all="ignore"):
+        out = ref_port.attack_model_replacement(X[0], g, int(c["num_clients"]), 10.0, 2)
+        assert np.array_equal(bits(out.numpy()), bits(c["out"]))
+        c = golden.case("attack_replace_boost")
+        out = ref_port.attack_model_replacement(X[0], g, 20, boost_factor=3.7)
+        assert np.array_equal(bits(out.numpy()), bits(c["out"]))
+        assert np.array_equal(bits(ref_port.attack_scaling(X[0], 100.0).numpy()), bits(golden.case("attack_scaling")["out"]))
+        assert np.array_equal(bits(ref_port.attack_ipm(X[0], 0.1).numpy()), bits(golden.case("attack_ipm_negate")["out"]))
+        assert np.array_equal(bits(ref_port.attack_ipm(X[1], 0.1, benign_mean=X[0]).numpy()),
+                              bits(golden.case("attack_ipm_sign")["out"]))
+        c = golden.case("attack_adaptive_krum")
+        out, center = ref_port.attack_adaptive_krum(X[1:], T(c["direction"]), 0.05)
+        assert np.array_equal(bits(center.numpy()), bits(c["center"]))
+        assert np.array_equal(bits(out.numpy()), bits(c["out"]))
 
 
 def test_median_stable_matches_torch_on_random_ties():

@@ -37,15 +37,16 @@ def test_shard_update_lists_views():
 def _worker(rank, world, port, X, f, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    from flagg.sharding import allreduce_partials, shard_update_lists
+    from flagg.sharding import shard_update_lists
+    from flagg.engine import all_reduce
     ups = [[torch.from_numpy(X[i])] for i in range(X.shape[0])]
     mine, (lo, hi) = shard_update_lists(ups, rank, world)
     Xs = np.stack([torch.cat(r).numpy() if r else np.zeros(0, np.float32) for r in mine])
     Xc = Xs.astype(np.float64) - Xs[0].astype(np.float64)
     G = torch.from_numpy(Xc @ Xc.T)
     stats = torch.from_numpy(oracle64.row_sumsq64(Xs))
-    allreduce_partials(G)
-    allreduce_partials(stats)
+    all_reduce(G, None)
+    all_reduce(stats, None)
     if rank == 0:
         out.put((G.numpy(), stats.numpy()))
     dist.barrier()
