@@ -54,6 +54,16 @@ def bits(a):
     return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
 
 
+def same_bits_nan_aware(got, ref):
+    """Bit-identical except that a NaN may carry any payload: x86 and the GPU propagate / generate
+    different NaN bit patterns through the same arithmetic (0x7FC00000 vs 0x7FFFFFFF); position and
+    NaN-ness must agree, every other value bit for bit."""
+    got = np.ascontiguousarray(got, dtype=np.float32)
+    ref = np.ascontiguousarray(ref, dtype=np.float32)
+    gn, rn = np.isnan(got), np.isnan(ref)
+    return got.shape == ref.shape and np.array_equal(gn, rn) and np.array_equal(bits(got)[~gn], bits(ref)[~rn])
+
+
 def assert_close_scaled(got, ref, scale, tol=1e-5, what=""):
     """|got-ref| <= tol*(|ref|+scale) per coordinate and ||got-ref|| <= tol*||ref||
     (SURVEY.md section 7 'Tolerance definition'); NaN/Inf positions must agree exactly."""
