@@ -10,6 +10,19 @@ Headline (BASELINE.json north_star / config 3): coordinate-wise median of a
 aggregation of that matrix.  GB/s = 4*n*d bytes of client updates aggregated per second;
 with N GPUs the parameter dimension is sharded (each rank owns its own 25M-column shard,
 weak scaling) and the median needs no communication.  One JSON line on stdout (rank 0).
+
+Beside the headline the line carries
+  roofline       the dominant kernel against the measured HBM rate
+  plugin_device  the same median through MedianDefense.aggregate on SEPARATELY ALLOCATED device
+                 rows (the run_experiments.py:238 layout: pointer-table view, no dense matrix)
+  e2e            the same median through the plugin call with pinned HOST tensors (Flower path)
+  e2e_pageable   Krum / FLTrust through the plugin call on pageable, separately allocated host
+                 tensors (the torch.tensor(ndarray) layout of robust_server.py:99-104)
+  strong         BASELINE configs 4 and 5 as STRONG scaling: the same 1000 x 25M Multi-Krum round
+                 and the same 500 x 11.69M FLTrust / clipping round column-sharded over the N ranks,
+                 timed through the plugin classes (all-reduce, selection and the K3 mean inside)
+  defenses       the other named shapes (C2) through the plugin classes, each with a CPU baseline
+  sharded_parity (N > 1) sharded selection == unsharded selection on every rank, checked before timing
 """
 import argparse
 import json
@@ -30,7 +43,11 @@ import torch  # noqa: E402
 
 METRIC = "aggregated client-update GB/s (coordinate-wise median, 100 clients x 25M params per GPU)"
 N_CLIENTS, D_PARAMS = 100, 25_000_000
-CPU_SAMPLE_COLS = 2_000_000
+WORKLOAD = "C3: 100 clients x 25,000,000 params per GPU, coordinate-wise median"
+CONFIG = {"workload": WORKLOAD, "n_clients": N_CLIENTS, "n_params_per_gpu": D_PARAMS,
+          "sharding": "parameter dimension over the GPUs, no collective for the median",
+          "l2_policy": "inputs (10 GB) larger than L2 (126 MB); no flush needed"}
+REF_BUDGET_S = 400.0        # the reference arm keeps its timed steps under about seven minutes (25 steps of <= 16 s)
 
 
 def peaks():
@@ -41,8 +58,18 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def bf16_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            j = json.load(fh)
+            return float(j.get("bf16_tflops", 0.0)), float(j.get("bf16_tflops_sustained", 0.0))
+    return 0.0, 0.0
+
+
 def tf32_peak_tflops():
-    """Dense TF32 GEMM rate of this GPU (library GEMM, used only as the roofline denominator)."""
+    """Dense TF32 GEMM rate of this GPU (library GEMM, used only as a roofline denominator):
+    best of 10 (burst) and the mean of 2 s back to back (sustained), with the SM clock sampled."""
     old = torch.backends.cuda.matmul.allow_tf32
     torch.backends.cuda.matmul.allow_tf32 = True
     a = torch.randn(8192, 8192, device="cuda")
@@ -55,9 +82,18 @@ def tf32_peak_tflops():
         e1.record()
         torch.cuda.synchronize()
         best = min(best, e0.elapsed_time(e1))
+    reps = max(10, int(2000.0 / best))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        torch.matmul(a, b)
+    e1.record()
+    torch.cuda.synchronize()
+    sustained = e0.elapsed_time(e1) / reps
     torch.backends.cuda.matmul.allow_tf32 = old
     del a, b
-    return 2.0 * 8192 ** 3 / best / 1e9
+    flop = 2.0 * 8192 ** 3
+    return flop / best / 1e9, flop / sustained / 1e9
 
 
 def ncu_traffic(kernel_key):
@@ -102,14 +138,21 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(rows)}
 
 
-def synth_rows(n, d, n_byz, seed, device="cuda"):
-    """Rows as run_experiments.py:238 produces them: full weights theta + delta_i; the first
-    n_byz rows are model-replacement style outliers theta + 10*delta (model_poisoning.py:65-80)."""
+def synth_rows(n, d, n_byz, seed, device="cuda", theta_sigma=0.05, spread=0.0):
+    """Rows as run_experiments.py:238 produces them: full weights theta + delta_i.  The first
+    n_byz rows are Byzantine: the reference's own ModelReplacementAttack (model_poisoning.py:48-80,
+    boost_factor = 10: theta + (x - theta) * 10) applied in place on the resident rows through the
+    attack mirror (flagg_segments_transform), not a hand-rolled formula."""
+    from src.attacks import ModelReplacementAttack
     g = torch.Generator(device=device).manual_seed(seed)
-    theta = torch.randn(d, device=device, generator=g) * 0.05
+    theta = torch.randn(d, device=device, generator=g) * theta_sigma
+    sig = 1e-3 * (1.0 + spread * (2 * torch.rand(n, generator=torch.Generator().manual_seed(seed)) - 1))
     X = torch.empty((n, d), dtype=torch.float32, device=device)
     for i in range(n):
-        X[i] = torch.randn(d, device=device, generator=g).mul_(1e-2 if i < n_byz else 1e-3).add_(theta)
+        X[i] = torch.randn(d, device=device, generator=g).mul_(float(sig[i])).add_(theta)
+    attack = ModelReplacementAttack({"boost_factor": 10.0})
+    for i in range(n_byz):
+        attack.poison_update([X[i]], [theta], n, out=[X[i]])
     return X
 
 
@@ -137,38 +180,406 @@ def time_steps(fn, steps, warmup, dist_on):
     return float(t.item())
 
 
-def cpu_reference_median(steps, warmup, n=N_CLIENTS, cols=CPU_SAMPLE_COLS):
-    """The reference's CPU path for this workload (torch.stack + torch.median(dim=0),
-    trimmed_mean.py:158-164) through the oracle port, on a bounded column sample."""
+# ---------------------------------------------------------------------------------------------
+# CPU legs: the reference's own algorithm on the host cores (oracle port; test infrastructure
+# used here only as the thing timed BESIDE the product, never inside it)
+# ---------------------------------------------------------------------------------------------
+def _cpu_rows(n, cols, seed=1234, n_byz=None, theta_sigma=0.05):
+    g = torch.Generator().manual_seed(seed)
+    theta = torch.randn(cols, generator=g) * theta_sigma
+    n_byz = n // 10 if n_byz is None else n_byz
+    return [[theta + torch.randn(cols, generator=g) * (1e-2 if i < n_byz else 1e-3)] for i in range(n)], theta
+
+
+def cpu_reference_median(steps, warmup, n=N_CLIENTS, cols=D_PARAMS, budget_s=None):
+    """The reference's CPU path for the headline workload (torch.stack + torch.median(dim=0),
+    trimmed_mean.py:158-164) through the oracle port, at the FULL 100 x 25M size.  With a time
+    budget the step counts are cut so the run still ends in minutes; the cut is returned."""
     from oracle import ref_port
     torch.set_num_threads(os.cpu_count() or 1)
-    g = torch.Generator().manual_seed(1234)
-    theta = torch.randn(cols, generator=g) * 0.05
-    rows = [[theta + torch.randn(cols, generator=g) * (1e-2 if i < 10 else 1e-3)] for i in range(n)]
+    rows, _ = _cpu_rows(n, cols)
+
     def step():
         stacked = torch.stack([u[0].float() for u in rows])      # the reference's packing copy is part of its path
         return ref_port.median(stacked)
-    for _ in range(warmup):
+    t0 = time.perf_counter()
+    step()                                                       # first warm-up, also sizes the rest of the run
+    first = time.perf_counter() - t0
+    if budget_s is not None:
+        afford = max(2, int(budget_s / max(first, 1e-3)))
+        warmup = min(warmup, max(1, afford // 5))
+        steps = min(steps, max(1, afford - warmup))
+    for _ in range(max(0, warmup - 1)):
         step()
     t0 = time.perf_counter()
     for _ in range(steps):
         step()
     dt = (time.perf_counter() - t0) / steps
-    return 4.0 * n * cols / dt / 1e9, dt, torch.get_num_threads()
+    return 4.0 * n * cols / dt / 1e9, dt, torch.get_num_threads(), steps, max(1, warmup)
+
+
+def cpu_trimmed_mean_c2():
+    """TrimmedMeanDefense at C2 full size (20 x 11,689,512, k = 2): stack + sort + slice + mean."""
+    from oracle import ref_port
+    torch.set_num_threads(os.cpu_count() or 1)
+    n, d = 20, 11_689_512
+    rows, _ = _cpu_rows(n, d, seed=2, n_byz=4)
+
+    def step():
+        return ref_port.trimmed_mean(torch.stack([u[0].float() for u in rows]), 0.1)
+    step()
+    t0 = time.perf_counter()
+    step()
+    dt = time.perf_counter() - t0
+    return {"value": 4.0 * n * d / dt / 1e9, "unit": "GB/s", "ms": dt * 1e3, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": "full size 20 x 11,689,512, 1 step after 1 warm-up (torch.stack + sort + slice + mean)"}
+
+
+def cpu_krum_extrapolated(n_full, d_full, n_sub=64, d_meas=3_125_000, f_frac=0.1):
+    """KrumDefense on n_sub of the n_full clients and d_meas of the d_full columns; the reference's
+    cost is the n(n-1)/2 loop of torch.norm(f_i - f_j) (krum.py:92-97), linear in the row length, so
+    the time is scaled by the pair count and the column count and LABELLED extrapolated."""
+    from oracle import ref_port
+    torch.set_num_threads(os.cpu_count() or 1)
+    rows, _ = _cpu_rows(n_sub, d_meas, seed=3, n_byz=max(1, int(n_sub * f_frac)))
+    X = torch.stack([u[0] for u in rows])
+    t0 = time.perf_counter()
+    ref_port.krum(X, max(1, int(n_sub * f_frac)), n_sub // 2)
+    dt = time.perf_counter() - t0
+    scale = (n_full * (n_full - 1)) / float(n_sub * (n_sub - 1)) * (d_full / float(d_meas))
+    est = dt * scale
+    return {"value": 4.0 * n_full * d_full / est / 1e9, "unit": "GB/s", "ms": est * 1e3, "cores": torch.get_num_threads(),
+            "kind": "port", "extrapolated": True,
+            "sample": f"{n_sub} of {n_full} clients x {d_meas} of {d_full} columns measured once ({dt:.2f} s), "
+                      f"scaled by pair count x column count = x{scale:.0f}"}
+
+
+def cpu_krum_full(n, d, f, multi_k):
+    from oracle import ref_port
+    torch.set_num_threads(os.cpu_count() or 1)
+    rows, _ = _cpu_rows(n, d, seed=4, n_byz=f)
+    X = torch.stack([u[0] for u in rows])
+    t0 = time.perf_counter()
+    ref_port.krum(X, f, multi_k)
+    dt = time.perf_counter() - t0
+    return {"value": 4.0 * n * d / dt / 1e9, "unit": "GB/s", "ms": dt * 1e3, "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"full size {n} x {d}, one call (flatten + n(n-1)/2 torch.norm + argsort + mean)"}
+
+
+def cpu_fltrust_sample(n, d, cols):
+    """FLTrustDefense trust scores + aggregate on a column sample of C5 (time scales with columns)."""
+    from oracle import ref_port
+    torch.set_num_threads(os.cpu_count() or 1)
+    rows, _ = _cpu_rows(n, cols, seed=5, n_byz=n // 10, theta_sigma=0.0)
+    X = torch.stack([u[0] for u in rows])
+    g0 = torch.randn(cols, generator=torch.Generator().manual_seed(6)) * 1e-3
+    X[n // 10:] += 0.7 * g0
+    t0 = time.perf_counter()
+    ref_port.fltrust(X, g0)
+    dt = time.perf_counter() - t0
+    est = dt * d / cols
+    return {"value": 4.0 * n * d / est / 1e9, "unit": "GB/s", "ms": est * 1e3, "cores": torch.get_num_threads(), "kind": "port",
+            "extrapolated": True,
+            "sample": f"{n} clients x {cols} of {d} columns measured once ({dt:.2f} s), scaled by the column count"}
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU legs beside the headline
+# ---------------------------------------------------------------------------------------------
+def separate_rows(X):
+    """One allocation per client (run_experiments.py:238: ``[p.data.clone() ...]``): rows at
+    unrelated addresses, so flagg_view_create cannot describe them as one dense matrix."""
+    return [[torch.empty(X.shape[1], dtype=torch.float32, device=X.device).copy_(X[i])] for i in range(X.shape[0])]
+
+
+def plugin_device_median(X, steps, dist_on, world):
+    """MedianDefense.aggregate on separately allocated device rows: Updates construction, pointer-table
+    upload, the per-row feed of K1, result split -- everything a caller of the plugin API pays."""
+    from src.defenses import MedianDefense
+    n, d = X.shape
+    ups = separate_rows(X)
+    defense = MedianDefense({})
+    t = time_steps(lambda: defense.aggregate(ups, [1] * n), steps, 3, dist_on) / steps
+    hbm, _ = peaks()
+    alg = 4.0 * d * (n + 1)
+    del ups
+    return {"ms": t * 1e3, "GBps": world * 4.0 * n * d / t / 1e9, "frac": alg / t / 1e9 / hbm, "steps": steps,
+            "api": "src.defenses.MedianDefense.aggregate(separately allocated device rows)",
+            "layout": "n separate device allocations (run_experiments.py:238)"}
+
+
+def e2e_median(X, out_dev, steps, dist_on, world):
+    """Pinned HOST tensors in, host tensors out, through MedianDefense.aggregate (Flower path,
+    robust_server.py:99-125): H2D of all n rows and D2H of the result inside the timed region."""
+    import torch.distributed as dist
+    from src.defenses import MedianDefense
+    n, d = X.shape
+    host = torch.empty((n, d), dtype=torch.float32, pin_memory=True)
+    host.copy_(X)
+    torch.cuda.synchronize()
+    if dist_on:
+        dist.barrier()
+    t0 = time.perf_counter()                                    # plain pinned H2D rate with every rank copying at once
+    X.copy_(host, non_blocking=True)
+    torch.cuda.synchronize()
+    pcie = torch.tensor([4.0 * n * d / (time.perf_counter() - t0) / 1e9], dtype=torch.float64, device="cuda")
+    pcie_all = [pcie.clone() for _ in range(world)] if dist_on else [pcie]
+    if dist_on:
+        dist.all_gather(pcie_all, pcie)
+    host_lists = [[host[i]] for i in range(n)]
+    defense = MedianDefense({})
+    defense.aggregate(host_lists, [1] * n)
+    if dist_on:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        res = defense.aggregate(host_lists, [1] * n)
+    torch.cuda.synchronize()
+    te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist_on:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    same = bool(torch.equal(res[0].view(torch.int32), out_dev.cpu().view(torch.int32)))
+    del host, host_lists, res
+    return {"value": world * 4.0 * n * d * steps / float(te.item()) / 1e9, "unit": "GB/s",
+            "h2d_bytes_per_step": 4 * n * d, "d2h_bytes_per_step": 4 * d, "steps": steps,
+            "api": "src.defenses.MedianDefense.aggregate(pinned host tensors)", "matches_device_result": same,
+            "pinned_h2d_memcpy_GBps_per_gpu_concurrent": [float(p.item()) for p in pcie_all]}
+
+
+def e2e_pageable(steps=3):
+    """Two-pass defenses on the Flower layout: every client's tensors are separate PAGEABLE host
+    allocations (robust_server.py:99-104, ``torch.tensor(arr)``); upload (worker threads gather into
+    pinned bounce buffers, 8 MB copies) + kernels + D2H of the result are all inside the timed region."""
+    from src.defenses import FLTrustDefense, KrumDefense
+
+    class Fixed(FLTrustDefense):
+        def _compute_server_gradient(self, global_params):
+            self.server_gradient = global_params
+            return global_params
+
+    n, seg = 20, [11_000_000, 689_512]
+    d = sum(seg)
+    g = torch.Generator().manual_seed(77)
+    theta = torch.randn(d, generator=g) * 0.05
+    ups = []
+    for i in range(n):
+        row = theta + torch.randn(d, generator=g) * (1e-2 if i < 4 else 1e-3)
+        ups.append([row[:seg[0]].clone(), row[seg[0]:].clone()])
+    g0 = [torch.randn(s, generator=g) * 1e-3 for s in seg]
+    out = {}
+    for name, fn in (("krum_20x11.69M_f4_m10", lambda: KrumDefense({"num_malicious": 4, "multi_k": 10}).aggregate(ups, [1] * n)),
+                     ("fltrust_20x11.69M", lambda: Fixed({}).aggregate(ups, [1] * n, global_params=g0))):
+        fn()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            fn()
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / steps
+        out[name] = {"value": 4.0 * n * d / dt / 1e9, "unit": "GB/s", "ms": dt * 1e3, "steps": steps,
+                     "h2d_bytes_per_step": 4 * n * d, "d2h_bytes_per_step": 4 * d,
+                     "layout": "pageable host tensors, one allocation per (client, tensor)"}
+    return out
+
+
+def sharded_parity_check(comm, rank, world):
+    """Before any timing at N > 1: the same seeded cohort on every rank, aggregated unsharded and
+    column-sharded through the communicator; selections must be identical, on every rank."""
+    import torch.distributed as dist
+    from flagg.sharding import shard_update_lists
+    from src.defenses import FLTrustDefense, MultiKrumDefense
+
+    class Fixed(FLTrustDefense):
+        def _compute_server_gradient(self, global_params):
+            self.server_gradient = global_params
+            return global_params
+
+    ok = True
+    for n, d, f, mk in ((20, 400_000, 4, 10), (200, 120_000, 20, 100)):
+        X = synth_rows(n, d, f, 4242, spread=0.3)
+        ups = [[X[i]] for i in range(n)]
+        a = MultiKrumDefense({"num_malicious": f, "multi_k": mk})
+        full = a.aggregate(ups, [1] * n)[0]
+        mine, (lo, hi) = shard_update_lists(ups, rank, world)
+        b = MultiKrumDefense({"num_malicious": f, "multi_k": mk, "process_group": comm})
+        part = torch.cat([t.reshape(-1) for t in b.aggregate(mine, [1] * n)])
+        ok &= a.selected_clients == b.selected_clients and a.rejected_clients == b.rejected_clients
+        ok &= bool(torch.equal(part.view(torch.int32), full[lo:hi].contiguous().view(torch.int32)))
+        g0 = [X[n - 1] - X[n - 2]]
+        ta, tb = Fixed({}), Fixed({"process_group": comm})
+        ta.aggregate(ups, [1] * n, global_params=g0)
+        tb.aggregate(mine, [1] * n, global_params=g0)
+        ok &= bool(np.allclose(ta.trust_scores, tb.trust_scores, rtol=0, atol=1e-6))
+        ok &= ta.detect_malicious(None, None) == tb.detect_malicious(None, None)
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    return bool(flag.item())
+
+
+def c2_defenses(dist_on, with_cpu):
+    """BASELINE config 2 through the plugin classes on separately allocated rows: trimmed mean
+    (r = 0.1 -> k = 2) and Krum (f = 4, the reference's default cohort regime) at 20 x 11,689,512."""
+    from src.defenses import KrumDefense, TrimmedMeanDefense
+    hbm, _ = peaks()
+    n, d = 20, 11_689_512
+    X = synth_rows(n, d, 4, 99, spread=0.3)
+    ups = separate_rows(X)
+    del X
+    out = {}
+    tm = TrimmedMeanDefense({"trim_ratio": 0.1})
+    t = time_steps(lambda: tm.aggregate(ups, [1] * n), 10, 3, dist_on) / 10
+    out["trimmed_mean_C2_20x11.69M_k2"] = {"n": n, "d": d, "ms": t * 1e3, "GBps": 4.0 * n * d / t / 1e9, "steps": 10,
+                                           "roofline_frac_hbm": 4.0 * d * (n + 1) / t / 1e9 / hbm,
+                                           "api": "TrimmedMeanDefense.aggregate(separately allocated device rows)"}
+    kd = KrumDefense({"num_malicious": 4, "multi_k": 1})
+    t = time_steps(lambda: kd.aggregate(ups, [1] * n), 10, 3, dist_on) / 10
+    out["krum_C2_20x11.69M_f4"] = {"n": n, "d": d, "ms": t * 1e3, "GBps": 4.0 * n * d / t / 1e9, "steps": 10,
+                                   "roofline_frac_hbm": 4.0 * n * d / t / 1e9 / hbm,
+                                   "api": "KrumDefense.aggregate(separately allocated device rows): centre + Gram + scores + argsort"}
+    del ups
+    if with_cpu:
+        out["trimmed_mean_C2_20x11.69M_k2"]["cpu_baseline"] = cpu_trimmed_mean_c2()
+        out["krum_C2_20x11.69M_f4"]["cpu_baseline"] = cpu_krum_full(20, 11_689_512, 4, 1)
+    return out
+
+
+def _alone_on_rank0(rank, dist_on, fn):
+    """Run ``fn`` on rank 0 only (the other ranks wait): the N = 1 point of a strong-scaling pair,
+    measured in the same job so the line can carry its own efficiency."""
+    import torch.distributed as dist
+    val = fn() if rank == 0 else None
+    torch.cuda.synchronize()
+    if dist_on:
+        dist.barrier()
+        box = [val]
+        dist.broadcast_object_list(box, src=0)
+        val = box[0]
+    return val
+
+
+def strong_scaling(rank, world, dist_on, comm, steps, with_cpu):
+    """BASELINE configs 4 and 5 as strong scaling: the SAME round column-sharded over the N ranks
+    (flagg.sharding.shard_bounds), timed through the plugin classes with ``process_group=comm``."""
+    from flagg import engine
+    from flagg.sharding import shard_bounds
+    from src.defenses import FLTrustDefense, GradientClippingDefense, MultiKrumDefense
+
+    class Fixed(FLTrustDefense):                 # g0 injected: the root-dataset SGD step is training, not aggregation
+        def _compute_server_gradient(self, global_params):
+            self.server_gradient = global_params
+            return global_params
+
+    hbm, _ = peaks()
+    out = {}
+    # ---------------- C4: 1000 x 25,000,000, Multi-Krum f = 100, multi_k = 900 ----------------
+    n, d, f, mk = 1000, 25_000_000, 100, 900
+    ne = [1] * n
+
+    def c4_time(cols, group, k, w, seed):
+        torch.cuda.empty_cache()
+        X = synth_rows(n, cols, f, seed, spread=0.3)
+        ups = [[X[i]] for i in range(n)]
+        defense = MultiKrumDefense({"num_malicious": f, "multi_k": mk, "process_group": group})
+        t = time_steps(lambda: defense.aggregate(ups, ne), k, w, dist_on and group is not None) / k
+        u = engine.Updates(ups)
+        tg = time_steps(lambda: engine.gram(u), 3, 1, False) / 3          # centre + local Gram kernel, no collective
+        u.close()
+        sel_ok = set(defense.rejected_clients[-f:]) == set(range(f))
+        del X, ups, u
+        return t, tg, sel_ok
+
+    lo, hi = shard_bounds(d, world)[rank]
+    t, tg, sel_ok = c4_time(hi - lo, comm, steps, 3, 31 + rank)
+    ar_us = None
+    if comm is not None:
+        G = torch.zeros((n, n), dtype=torch.float64, device="cuda")
+        ar_us = time_steps(lambda: comm.all_reduce(G), 20, 3, True) / 20 * 1e6
+        del G
+    tf32_burst, tf32_sust = tf32_peak_tflops()
+    bf16_burst, bf16_sust = bf16_peak()
+    flops = float(n) * (n + 1) * (hi - lo)
+    c4 = {"workload": "C4: 1000 clients x 25,000,000 params, Multi-Krum f=100 multi_k=900, one round",
+          "api": "MultiKrumDefense.aggregate(process_group=flagg.Comm): centre + Gram + all-reduce + scores + argsort + mean of 900 rows",
+          "n_gpus": world, "cols_per_gpu": hi - lo, "steps": steps, "ms": t * 1e3, "GBps": 4.0 * n * d / t / 1e9,
+          "clients_x_params_per_s": n * d / t, "gram_ms_local": tg * 1e3, "allreduce_8MB_f64_us": ar_us,
+          "byzantine_rows_ranked_last": sel_ok,
+          "roofline": {"bound": "tensor", "kernel": "gram_ts2_kernel (tcgen05 cta_group::2 kind::tf32, 3 products per k-step)",
+                       "achieved": flops / tg / 1e12, "unit": "TFLOP/s", "algorithmic_flops_per_launch": flops,
+                       "peak_tf32_over_3_burst": tf32_burst / 3, "peak_tf32_over_3_sustained": tf32_sust / 3,
+                       "peak_bf16_over_6_burst": bf16_burst / 6, "peak_bf16_over_6_sustained": bf16_sust / 6,
+                       "frac": flops / tg / 1e12 / (tf32_burst / 3),
+                       "frac_vs_bf16_over_6": (flops / tg / 1e12 / (bf16_burst / 6)) if bf16_burst else None,
+                       "tf32_dense_measured_burst": tf32_burst, "tf32_dense_measured_sustained": tf32_sust}}
+    if world > 1:
+        t1 = _alone_on_rank0(rank, dist_on, lambda: c4_time(d, None, 5, 2, 31)[0])
+        c4["t1_ms_rank0_alone"] = t1 * 1e3
+        c4["efficiency"] = t1 / (world * t)
+    else:
+        c4["efficiency"] = 1.0
+    if with_cpu:
+        c4["cpu_baseline"] = cpu_krum_extrapolated(n, d)
+    out["c4"] = c4
+    # ---------------- C5: 500 x 11,689,512, FLTrust and gradient clipping ----------------
+    n, d = 500, 11_689_512
+    ne = [50 + (i % 7) for i in range(n)]
+    g0_full = torch.randn(d, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5)) * 1e-3
+
+    def c5_time(cols_lo, cols_hi, group, k, w, seed):
+        torch.cuda.empty_cache()
+        X = synth_rows(n, cols_hi - cols_lo, n // 10, seed, theta_sigma=0.0, spread=0.3)
+        X[n // 10:] += 0.7 * g0_full[cols_lo:cols_hi]
+        ups = [[X[i]] for i in range(n)]
+        g0 = [g0_full] if group is not None else [g0_full[cols_lo:cols_hi]]
+        on = dist_on and group is not None
+        fl = Fixed({"process_group": group})
+        tf = time_steps(lambda: fl.aggregate(ups, ne, global_params=g0), k, w, on) / k
+        clip = float(np.median(np.sqrt(engine.row_stats(engine.Updates(ups), group=group)["sumsq"])))
+        gc = GradientClippingDefense({"clip_norm": clip, "clip_type": "l2", "process_group": group})
+        tc = time_steps(lambda: gc.aggregate(ups, ne), k, w, on) / k
+        ok = bool(np.all(np.array(fl.trust_scores[n // 10:]) > 0.1)) and 0 < gc.clipped_count < n
+        del X, ups
+        return tf, tc, ok
+
+    lo, hi = shard_bounds(d, world)[rank]
+    tf, tc, ok = c5_time(lo, hi, comm, steps, 3, 51 + rank)
+    alg = 4.0 * (hi - lo) * (2 * n + 2)
+    c5 = {"workload": "C5: 500 clients x 11,689,512 params, FLTrust (injected g0) and GradientClipping L2, one round each",
+          "n_gpus": world, "cols_per_gpu": hi - lo, "steps": steps, "sane": ok,
+          "fltrust": {"api": "FLTrustDefense.aggregate(process_group=flagg.Comm, global_params=g0)", "ms": tf * 1e3,
+                      "GBps": 4.0 * n * d / tf / 1e9, "roofline_frac_hbm": alg / tf / 1e9 / hbm},
+          "gradient_clipping": {"api": "GradientClippingDefense.aggregate(process_group=flagg.Comm)", "ms": tc * 1e3,
+                                "GBps": 4.0 * n * d / tc / 1e9, "roofline_frac_hbm": 4.0 * (hi - lo) * (2 * n + 1) / tc / 1e9 / hbm},
+          "algorithmic_bytes_per_gpu": alg}
+    if world > 1:
+        t1 = _alone_on_rank0(rank, dist_on, lambda: c5_time(0, d, None, 5, 2, 51)[:2])
+        c5["fltrust"]["t1_ms_rank0_alone"], c5["gradient_clipping"]["t1_ms_rank0_alone"] = t1[0] * 1e3, t1[1] * 1e3
+        c5["fltrust"]["efficiency"] = t1[0] / (world * tf)
+        c5["gradient_clipping"]["efficiency"] = t1[1] / (world * tc)
+        c5["efficiency"] = c5["fltrust"]["efficiency"]
+    else:
+        c5["efficiency"] = 1.0
+    if with_cpu:
+        c5["cpu_baseline"] = cpu_fltrust_sample(n, d, 1_000_000)
+    del g0_full
+    out["c5"] = c5
+    return out
 
 
 def run_reference(args, rank):
+    """The reference's CPU implementation of the headline workload on the host cores, the SAME
+    100 x 25M step as the GPU arm (no column sample); --steps / --warmup are honoured unless the
+    projected run exceeds REF_BUDGET_S, in which case the counts used are stated in the line."""
     if rank != 0:
         return
-    steps, warm = max(1, min(args.steps, 5)), max(1, min(args.warmup, 2))
-    gbs, dt, cores = cpu_reference_median(steps, warm)
-    sample = f"{N_CLIENTS} clients x {CPU_SAMPLE_COLS} of {D_PARAMS} columns per step (torch CPU, all host threads)"
+    gbs, dt, cores, steps, warm = cpu_reference_median(args.steps, args.warmup, budget_s=REF_BUDGET_S)
+    sample = f"full step: {N_CLIENTS} clients x {D_PARAMS} columns (torch CPU, all host threads), {dt:.2f} s/step"
+    clamp = None
+    if steps != args.steps or warm != args.warmup:
+        clamp = f"ran {steps} steps after {warm} warm-ups (requested {args.steps}/{args.warmup}) to stay under {REF_BUDGET_S:.0f} s"
     line = {
         "impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": args.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C3: 100 clients x 25,000,000 params, coordinate-wise median (bounded column sample)",
-                   "n_clients": N_CLIENTS, "n_params": D_PARAMS},
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": dict(CONFIG), "clamp": clamp,
         "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -176,76 +587,22 @@ def run_reference(args, rank):
     emit(line)
 
 
-def extra_defenses(rank, world, dist_on, group):
-    """Other defenses of the path, short runs (not the headline): trimmed mean (C2),
-    FLTrust + clipping stages (C5) and the Krum Gram (C2 cohort, C4 shard).  GB/s = 4*n*d/t."""
-    from flagg import TRIMMED_MEAN, engine
-    hbm, _ = peaks()
-    out = {}
-
-    def bench(name, n, d, fn_factory, alg_bytes, steps=3):
-        torch.cuda.empty_cache()
-        X = synth_rows(n, d, max(1, n // 10), 99 + rank)
-        u = engine.Updates([[X[i]] for i in range(n)])
-        fn = fn_factory(u, X)
-        t = time_steps(fn, steps, 3, dist_on) / steps
-        out[name] = {"n": n, "d_per_gpu": d, "ms": t * 1e3, "GBps": world * 4.0 * n * d / t / 1e9,
-                     "clients_x_params_per_s": world * n * d / t,
-                     "roofline_frac_hbm": (alg_bytes / t / 1e9) / hbm}
-        u.close()
-        del X, u
-
-    bench("trimmed_mean_C2_20x11.69M_k2", 20, 11_689_512,
-          lambda u, X: (lambda: engine.colwise_select(u, TRIMMED_MEAN, 2)), 4.0 * 11_689_512 * 21)
-    n5, d5 = 500, 11_689_512
-    g0 = torch.randn(d5, device="cuda") * 1e-3
-
-    def fltrust_factory(u, X):
-        w = np.ones(n5, dtype=np.float32)
-        def step():
-            st = engine.row_stats(u, g0, group=group)            # K2 (+ all-reduce of 2n+1 doubles when sharded)
-            sc = (np.sqrt(st["g0_sumsq"]) / np.sqrt(st["sumsq"])).astype(np.float32)
-            engine.row_combine(u, None, sc, w, float(n5))         # K3
-        return step
-    bench("fltrust_C5_500x11.69M", n5, d5, fltrust_factory, 4.0 * d5 * (2 * n5 + 2))
-    def krum_c2_factory(u, X):
-        def step():
-            G = engine.gram(u, group=group)         # K4, small-cohort kernel (gram_small.cu)
-            engine.krum_scores(G, 5, want_D=False)                # K5
-        return step
-    bench("krum_gram_C2_20x11.69M_f5", 20, 11_689_512, krum_c2_factory, 4.0 * 20 * 11_689_512, steps=5)
-    n4, d4 = 1000, 25_000_000 // 8
-
-    def krum_factory(u, X):
-        def step():
-            G = engine.gram(u, group=group)         # K4 (+ all-reduce of the n x n FP64 Gram)
-            engine.krum_scores(G, 100, want_D=False)              # K5
-        return step
-    bench("multikrum_gram_C4shard_1000x3.125M_f100", n4, d4, krum_factory, 4.0 * n4 * d4, steps=3)
-    gk = out["multikrum_gram_C4shard_1000x3.125M_f100"]
-    # tensor roofline of the Gram kernel: algorithmic flops n(n+1)d (unique pairs, mul+add) against
-    # exact-FP32-by-3xTF32 peak = measured dense TF32 GEMM rate / 3 (cuBLAS 8192^3, best of 10, same process)
-    tf32 = tf32_peak_tflops()
-    gk["TFLOPs_alg"] = world * n4 * (n4 + 1) * d4 / (gk["ms"] / 1e3) / 1e12
-    gk["roofline"] = {"bound": "tensor", "achieved": gk["TFLOPs_alg"] / world, "peak": tf32 / 3.0, "unit": "TFLOP/s",
-                      "frac": gk["TFLOPs_alg"] / world / (tf32 / 3.0), "tf32_dense_measured": tf32,
-                      "kernel": "gram_ts2_kernel (tcgen05 cta_group::2 kind::tf32, 256x256 CTA-pair tiles, A from TMEM, 3 products per k-step)"}
-    return out
-
-
 def run_flagg(args, rank, world, local_rank):
     import torch.distributed as dist
     from flagg import MEDIAN, engine
-    from src.defenses import MedianDefense
+    from flagg._lib import check, lib
     dist_on = world > 1
     torch.cuda.set_device(local_rank)
     if dist_on:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    # the sharded defenses' one collective goes through the C-ABI communicator (flagg_comm: NCCL), its id over torch.distributed
+    comm = engine.Comm.from_torch() if dist_on else None
+    parity = sharded_parity_check(comm, rank, world) if dist_on else None
+
     n, d = N_CLIENTS, D_PARAMS
     X = synth_rows(n, d, 10, 1234 + rank)
     u = engine.Updates([[X[i]] for i in range(n)])
     out = torch.empty(d, dtype=torch.float32, device="cuda")
-    from flagg._lib import check, lib
     stream = torch.cuda.current_stream().cuda_stream
     view = u.view()
 
@@ -262,40 +619,22 @@ def run_flagg(args, rank, world, local_rank):
     hbm, which = peaks()
     alg_bytes = 4.0 * d * (n + 1)
     achieved = alg_bytes / (t / args.steps) / 1e9
+    launches = args.steps
 
-    # end to end through the plugin API with pinned HOST tensors in and host tensors out
-    # (Flower path, robust_server.py:99-125): H2D of all n rows and D2H of the result inside the timed region
-    e2e, same, e2e_steps, pcie = None, None, 0, None
-    if not args.no_e2e:
-        host = torch.empty((n, d), dtype=torch.float32, pin_memory=True)
-        host.copy_(X)
-        torch.cuda.synchronize()
-        # plain pinned H2D rate of this box = the ceiling of any host-input path
-        t0 = time.perf_counter()
-        X.copy_(host, non_blocking=True)
-        torch.cuda.synchronize()
-        pcie = 4.0 * n * d / (time.perf_counter() - t0) / 1e9
-        host_lists = [[host[i]] for i in range(n)]
-        defense = MedianDefense({})
-        e2e_steps = max(1, min(args.steps, 3))
-        defense.aggregate(host_lists, [1] * n)
+    plugin = plugin_device_median(X, 10, dist_on, world) if not args.no_extras else None
+    e2e = e2e_median(X, out, max(1, min(args.steps, 3)), dist_on, world) if not args.no_e2e else None
+    u.close()
+    del X, u, out
+    torch.cuda.empty_cache()
+    with_cpu = world == 1 and not args.no_cpu
+    extras, strong, pageable = {}, None, None
+    if not args.no_extras:
+        if rank == 0:
+            pageable = e2e_pageable() if not args.no_e2e else None
+            extras = c2_defenses(False, with_cpu)
         if dist_on:
             dist.barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            res = defense.aggregate(host_lists, [1] * n)
-        torch.cuda.synchronize()
-        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-        if dist_on:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e = world * 4.0 * n * d * e2e_steps / float(te.item()) / 1e9
-        same = bool(torch.equal(res[0].view(torch.int32), out.cpu().view(torch.int32)))
-        del host, host_lists, res
-    u.close()
-    del X, u
-    # the sharded defenses' one collective goes through the C-ABI communicator (flagg_comm: NCCL), its id over torch.distributed
-    comm = engine.Comm.from_torch() if (dist_on and not args.no_extras) else None
-    extras = extra_defenses(rank, world, dist_on, comm) if not args.no_extras else {}
+        strong = strong_scaling(rank, world, dist_on, comm, max(10, min(args.steps, 20)), with_cpu)
     if comm is not None:
         comm.close()
 
@@ -303,23 +642,20 @@ def run_flagg(args, rank, world, local_rank):
         line = {
             "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C3: 100 clients x 25,000,000 params per GPU, coordinate-wise median",
-                       "n_clients": n, "n_params_per_gpu": d, "sharding": f"parameter dim x{world}, no collective",
-                       "l2_policy": "inputs (10 GB) larger than L2 (126 MB); no flush needed",
-                       "clients_x_params_per_s": world * n * d * args.steps / t},
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic (Byzantine rows: the reference's ModelReplacementAttack through the attack mirror)",
+            "config": dict(CONFIG), "clients_x_params_per_s": world * n * d * args.steps / t,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                          "traffic": ncu_traffic("colselect_bulk_kernel<100,median>"), "peak_source": which,
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel": "colselect_bulk_kernel<100, MEDIAN_EXACT> (2-D TMA feed; the input is one dense matrix)"},
-            "e2e": {"value": e2e, "unit": "GB/s", "h2d_bytes_per_step": 4 * n * d, "d2h_bytes_per_step": 4 * d,
-                    "steps": e2e_steps, "api": "src.defenses.MedianDefense.aggregate(pinned host tensors)",
-                    "matches_device_result": same, "pinned_h2d_memcpy_GBps": pcie},
-            "gpu_launches": args.steps, "clocks": clocks, "defenses": extras,
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "plugin_device": plugin, "e2e_pageable": pageable, "strong": strong, "defenses": extras,
         }
-        if world == 1 and not args.no_cpu:
-            gbs, dt, cores = cpu_reference_median(1, 1)
+        if dist_on:
+            line["sharded_parity"] = parity
+        if with_cpu:
+            gbs, dt, cores, _, _ = cpu_reference_median(1, 1)
             line["cpu_baseline"] = {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port",
-                                    "sample": f"{n} clients x {CPU_SAMPLE_COLS} of {d} columns, 1 step after 1 warm-up "
+                                    "sample": f"full step {n} clients x {d} columns, 1 step after 1 warm-up "
                                               f"(oracle port of torch.stack+torch.median, {dt:.2f} s/step)"}
         emit(line)
     if dist_on:
