@@ -158,13 +158,14 @@ extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float*
         // TMA-staged feed for the exact sizes on 16-byte aligned tensors; FLAGG_K1_IMPL=ldg|bulk overrides (tests, tuning)
         const char* impl = getenv("FLAGG_K1_IMPL");
         const bool want_bulk = impl ? !strcmp(impl, "bulk") : true;
-        if (impl && !strcmp(impl, "bulk") && !(exact && v->align_bytes >= 16)) {
-            set_error("flagg_colwise_select: FLAGG_K1_IMPL=bulk needs n in the generated sizes and 16-byte aligned tensors");
+        if (impl && !strcmp(impl, "bulk") && !(exact && (v->dense || v->gather))) {
+            set_error("flagg_colwise_select: FLAGG_K1_IMPL=bulk needs n in the generated sizes and a dense or 512-byte-congruent view");
             return FLAGG_EUNSUPPORTED;
         }
-        const bool force_bulk = impl && !strcmp(impl, "bulk");
-        const int flag = (want_bulk && exact && v->align_bytes >= 16 && (v->dense || force_bulk)) ? CS_BULK : 0;
-        return e->fn(v->dev, variant | flag, k, out, units, sms, st);
+        // dense matrix -> one 2-D box per tile; separately allocated 512-byte-congruent rows -> gather4 (four clients per request)
+        const int flag = (want_bulk && exact && v->align_bytes >= 16 && (v->dense || v->gather)) ? CS_BULK : 0;
+        const bool wide = flag && !v->dense && v->dev.gather_cols == 256 && e->n <= CSB_WIDE_MAX_N;
+        return e->fn(v->dev, variant | flag | (wide ? CS_WIDE : 0), k, out, wide ? v->total_units[GRAN_256] : units, sms, st);
     }
     {   // shared-memory tile select (colselect_tile.cu): one HBM read instead of 8-17.  Measured against the radix
         // fallback (tools/k1_large_n.py, profiles/r01_k1_large_n.txt) it wins for the median up to n ~ 1500 and for

@@ -34,12 +34,21 @@ void set_error(const char* fmt, ...);
 struct ViewDev {
     const float* const* seg_ptrs;  // [n*P]  seg_ptrs[i*P+p]
     const int64_t* seg_start;      // [P+1]  column prefix; seg_start[P] == d
-    const int64_t* unit_start[3];  // [P+1] each: prefix of UNIT_COLS[g]-wide column units per segment
+    const int64_t* unit_start[4];  // [P+1] each: prefix of UNIT_COLS[g]-wide column units per segment
     int n, P;
     int64_t d;
     // CUtensorMap[P] (64 B each, device memory) when every tensor is one dense [n x len] matrix
     // with a 16-byte-multiple row pitch -- box {128 columns, n rows}; nullptr otherwise.
     const void* tmaps;
+    // Separately allocated rows (the reference's list-of-lists, run_experiments.py:238): ONE CUtensorMap
+    // over the address range [min pointer, max end) seen as a 2-D fp32 matrix of 128-column (512-byte)
+    // rows, and seg_rows[p][i] = (seg_ptrs[i*P+p] - min pointer) / 512 ([P][n rounded up to 4], padded with client n-1).  A 128-column unit of any
+    // tensor of any client is then one row of that matrix, and cp.async.bulk.tensor.2d.tile::gather4
+    // brings four clients' units per TMA request.  nullptr unless every tensor base is 512-byte aligned
+    // (what PyTorch's allocator returns for separately allocated tensors) and the range fits 2^31 rows.
+    const void* gmap;
+    const int32_t* seg_rows;
+    int gather_cols;               // columns per gmap row box: 256 (rows overlap: pitch 512 B, extent 1 KB) or 128
     // Round-epilogue form (flagg_view_set_outputs): when non-NULL, kernels that produce a [d] result
     // write tensor p of it to out_ptrs[p] (the global model's own parameter tensors) instead of
     // out + seg_start[p] -- the inverse of seg_ptrs; replaces the per-tensor param.copy_(new_val)
@@ -54,9 +63,9 @@ __device__ __forceinline__ float* out_addr(const ViewDev& v, float* out, int p, 
 
 // Work is indexed in "units": runs of UNIT_COLS[g] columns that never cross a segment
 // (tensor) boundary.  Three granularities serve the three kernel families.
-constexpr int NUM_GRAN = 3;
-constexpr int GRAN_128 = 0, GRAN_1K = 1, GRAN_2K = 2;
-__host__ __device__ constexpr int unit_cols(int g) { return g == 0 ? 128 : (g == 1 ? 1024 : 2048); }
+constexpr int NUM_GRAN = 4;
+constexpr int GRAN_128 = 0, GRAN_1K = 1, GRAN_2K = 2, GRAN_256 = 3;
+__host__ __device__ constexpr int unit_cols(int g) { return g == 0 ? 128 : (g == 1 ? 1024 : (g == 2 ? 2048 : 256)); }
 
 int device_sm_count();
 
@@ -74,7 +83,8 @@ struct flagg_view {
     size_t scratch_bytes = 0;
     int align_bytes = 4;           // min alignment over all segment base addresses (4/8/16)
     bool dense = false;            // dev.tmaps is valid (see ViewDev::tmaps)
-    int64_t total_units[flagg::NUM_GRAN] = {0, 0, 0};
+    bool gather = false;           // dev.gmap / dev.seg_rows are valid (see ViewDev::gmap)
+    int64_t total_units[flagg::NUM_GRAN] = {0, 0, 0, 0};
     int device = 0;
     void* last_stream = nullptr;   // stream of the latest call on this view: frees are ordered on it
     int ensure_scratch(size_t bytes);

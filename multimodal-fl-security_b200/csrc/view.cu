@@ -3,6 +3,7 @@
 #include <cuda.h>
 #include <cudaTypedefs.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -150,11 +151,66 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
         v->dense = ok;
     }
 
+    // Gather map for rows that are NOT one matrix (see ViewDev::gmap).
+    CUtensorMap gmap[2];      // [0] 256-column overlapped rows (when the encoder takes them), [1] 128-column rows
+    std::vector<int32_t> seg_rows;
+    memset(gmap, 0, sizeof(gmap));
+    if (!v->dense && n >= 2 && n <= 256 && align == 16) {
+        PFN_cuTensorMapEncodeTiled_v12000 encode = tensor_map_encoder();
+        uintptr_t lo = ~uintptr_t(0), hi = 0;
+        for (size_t i = 0; i < v->seg_ptrs.size(); ++i) {
+            if (v->seg_numel[i % P] == 0) continue;
+            const uintptr_t a = reinterpret_cast<uintptr_t>(v->seg_ptrs[i]);
+            lo = a < lo ? a : lo;
+            const uintptr_t end = a + ((uintptr_t(v->seg_numel[i % P]) * 4 + 511) & ~uintptr_t(511));
+            hi = end > hi ? end : hi;
+        }
+        bool ok = encode != nullptr && hi > lo && ((hi - lo) >> 9) < (uintptr_t(1) << 31);
+        const int npad = (n + 3) & ~3;                      // transposed [P][npad]: one 16-byte load per gather4 request
+        seg_rows.assign(size_t(P) * npad, 0);
+        for (size_t i = 0; i < v->seg_ptrs.size() && ok; ++i) {
+            if (v->seg_numel[i % P] == 0) continue;
+            // truly 512-byte aligned (not merely congruent): a tensor's ragged last unit is then read to the end of a
+            // 512-byte granule that holds valid data, which no allocation boundary or page boundary can cut
+            const uintptr_t a = reinterpret_cast<uintptr_t>(v->seg_ptrs[i]);
+            ok = (a & 511) == 0;
+            seg_rows[(i % P) * npad + i / P] = int32_t((a - lo) >> 9);
+        }
+        for (int p = 0; p < P; ++p)
+            for (int i = n; i < npad; ++i) seg_rows[size_t(p) * npad + i] = seg_rows[size_t(p) * npad + n - 1];
+        if (ok) {
+            // Rows of 256 columns at a 512-byte pitch (consecutive rows overlap by half): a 256-column unit of a tensor
+            // is row seg_rows + 2 * unit, and a gather4 request carries 4 KB.  The last row is kept inside the range.
+            // FLAGG_K1_GATHER_COLS=128 selects plain 128-column rows (2 KB per request; tuning / tests).
+            const char* gc = getenv("FLAGG_K1_GATHER_COLS");
+            const cuuint64_t rows = cuuint64_t((hi - lo) >> 9);
+            const cuuint64_t gstride[1] = {512u};
+            const cuuint32_t estride[2] = {1u, 1u};
+            v->dev.gather_cols = 128;
+            const cuuint64_t gdim1[2] = {128u, rows};
+            const cuuint32_t box1[2] = {128u, 1u};         // tile::gather4: four such rows per request
+            CUresult r = encode(&gmap[1], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, reinterpret_cast<void*>(lo), gdim1, gstride, box1, estride,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r == CUDA_SUCCESS && !(gc && atoi(gc) == 128) && rows >= 2) {
+                const cuuint64_t gdim2[2] = {256u, rows - 1};
+                const cuuint32_t box2[2] = {256u, 1u};
+                if (encode(&gmap[0], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, reinterpret_cast<void*>(lo), gdim2, gstride, box2, estride,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS)
+                    v->dev.gather_cols = 256;
+            }
+            ok = (r == CUDA_SUCCESS);
+        }
+        v->gather = ok;
+    }
+
     const size_t b_ptrs = sizeof(void*) * size_t(n) * P;
     const size_t b_pref = sizeof(int64_t) * (P + 1);
-    const size_t b_tabs = (b_ptrs + (1 + NUM_GRAN) * b_pref + 63) & ~size_t(63);   // tensor maps need 64-byte alignment
-    const size_t b_tmaps = v->dense ? sizeof(CUtensorMap) * P : 0;
-    const size_t total = b_tabs + b_tmaps + sizeof(void*) * P;   // tail: output pointer table (flagg_view_set_outputs)
+    const size_t b_tabs = (b_ptrs + (1 + NUM_GRAN) * b_pref + 127) & ~size_t(127);   // tensor maps need 64-byte alignment
+    const size_t b_tmaps = v->dense ? sizeof(CUtensorMap) * P : (v->gather ? 2 * sizeof(CUtensorMap) : 0);
+    const size_t b_rows = v->gather ? sizeof(int32_t) * seg_rows.size() : 0;   // a multiple of 16 bytes
+    const size_t total = b_tabs + b_tmaps + b_rows + sizeof(void*) * P;   // tail: output pointer table (flagg_view_set_outputs)
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     v->last_stream = stream;
     if (pool_ready(v->device) != FLAGG_OK) { delete v; return FLAGG_ECUDA; }
@@ -169,6 +225,11 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
         e = cudaMemcpyAsync(base + b_ptrs + (1 + g) * b_pref, v->unit_start[g].data(), b_pref, cudaMemcpyHostToDevice, st);
     if (e == cudaSuccess && v->dense)
         e = cudaMemcpyAsync(base + b_tabs, tmaps.data(), sizeof(CUtensorMap) * P, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && v->gather) {
+        e = cudaMemcpyAsync(base + b_tabs, gmap, 2 * sizeof(CUtensorMap), cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(base + b_tabs + b_tmaps, seg_rows.data(), b_rows, cudaMemcpyHostToDevice, st);
+    }
     if (e != cudaSuccess) {
         set_error("flagg_view_create: table upload failed: %s", cudaGetErrorString(e));
         cudaFreeAsync(v->d_tables, st);
@@ -180,7 +241,9 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
     for (int g = 0; g < NUM_GRAN; ++g)
         v->dev.unit_start[g] = reinterpret_cast<const int64_t*>(base + b_ptrs + (1 + g) * b_pref);
     v->dev.tmaps = v->dense ? base + b_tabs : nullptr;
-    v->d_out_ptrs = base + b_tabs + b_tmaps;
+    v->dev.gmap = v->gather ? base + b_tabs : nullptr;
+    v->dev.seg_rows = v->gather ? reinterpret_cast<const int32_t*>(base + b_tabs + b_tmaps) : nullptr;
+    v->d_out_ptrs = base + b_tabs + b_tmaps + b_rows;
     v->dev.out_ptrs = nullptr;
     v->dev.n = n;
     v->dev.P = P;

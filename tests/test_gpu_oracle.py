@@ -101,6 +101,66 @@ def test_median_and_trimmed_dense_tma_path(n, impl, monkeypatch):
     u.close()
 
 
+@pytest.mark.parametrize("gather_cols", ["256", "128"])
+@pytest.mark.parametrize("n", [2, 3, 5, 10, 20, 31, 33, 64, 100, 110, 112, 128])
+def test_median_and_trimmed_gather4_path(n, gather_cols, monkeypatch):
+    """K1 on SEPARATELY ALLOCATED rows (one allocation per (client, tensor), 512-byte aligned: the
+    reference's list-of-lists, run_experiments.py:238): the tile is fed by tile::gather4 requests through
+    the view-wide tensor maps -- 256-column overlapped rows (4 KB per request) or 128-column rows.
+    Covers n not a multiple of 4 (padding rows), ragged last units with <= 128 and > 128 columns left
+    (the per-row fallback inside the wide kernel), tiny tensors, and must equal the LDG feed bit for bit."""
+    from flagg import MEDIAN, TRIMMED_MEAN, engine
+    monkeypatch.setenv("FLAGG_K1_GATHER_COLS", gather_cols)
+    monkeypatch.delenv("FLAGG_K1_IMPL", raising=False)
+    rng = np.random.RandomState(5000 + n)
+    seg = [256 * 3 + 130, 7, 128, 256 * 2 + 100, 255, 257, 1]
+    d = sum(seg)
+    X = rows_model(rng, n, d, byz=n // 5)
+    X[:, :150] = rng.choice(EDGE, size=(n, 150))
+    X[:, 150:182] = rng.choice(np.array([0.0, -0.0], dtype=np.float32), size=(n, 32))
+    Xi = X.view(np.uint32)
+    for j in range(182, 200):
+        Xi[rng.randint(n), j] = rng.choice([0x7FC00000, 0xFFC00001, 0x7F800123])
+    ups = dev_lists(X, seg)
+    assert all(t.data_ptr() % 512 == 0 for row in ups for t in row)
+    u = engine.Updates(ups)
+    got = engine.colwise_select(u, MEDIAN).cpu().numpy()
+    assert np.array_equal(bits(got), bits(oracle64.median_stable(X))), (n, gather_cols)
+    monkeypatch.setenv("FLAGG_K1_IMPL", "ldg")
+    assert np.array_equal(bits(got), bits(engine.colwise_select(u, MEDIAN).cpu().numpy()))
+    monkeypatch.delenv("FLAGG_K1_IMPL")
+    k = max(1, n // 10)
+    if n - 2 * k >= 1:
+        Xt = X.copy()
+        Xt[:, :200] = rows_model(rng, n, 200)
+        u2 = engine.Updates(dev_lists(Xt, seg))
+        gt = engine.colwise_select(u2, TRIMMED_MEAN, k).cpu().numpy()
+        assert_close_scaled(gt, oracle64.trimmed_mean64(Xt, k), oracle64.trimmed_scale(Xt, k), tol=2e-6, what=f"n={n} k={k}")
+        u2.close()
+    u.close()
+
+
+def test_gather_map_needs_512_byte_alignment_else_ldg():
+    """Rows at a 16-byte offset inside their allocations cannot use the gather map (a ragged last
+    unit could be read past its granule); the view falls back to the LDG feed and FLAGG_K1_IMPL=bulk
+    says so instead of silently doing something else."""
+    from flagg import FlaggError, MEDIAN, engine
+    import os
+    rng = np.random.RandomState(77)
+    n, d = 20, 1000
+    X = rows_model(rng, n, d)
+    ups = [[torch.zeros(d + 4, device="cuda")[4:].copy_(torch.from_numpy(X[i]))] for i in range(n)]
+    u = engine.Updates(ups)
+    assert np.array_equal(bits(engine.colwise_select(u, MEDIAN).cpu().numpy()), bits(oracle64.median_stable(X)))
+    os.environ["FLAGG_K1_IMPL"] = "bulk"
+    try:
+        with pytest.raises(FlaggError):
+            engine.colwise_select(u, MEDIAN)
+    finally:
+        del os.environ["FLAGG_K1_IMPL"]
+    u.close()
+
+
 @pytest.mark.parametrize("impl", ["tile", "radix"])
 @pytest.mark.parametrize("n", [129, 130, 131, 200, 257, 1000, 2047])
 def test_median_large_n_tile_and_radix(n, impl, monkeypatch):
