@@ -156,6 +156,18 @@ int flagg_weiszfeld_weights(const double* sumsq, int n, float* w, float* wsum, v
  * `accumulate` != 0 adds into G instead of overwriting it. */
 int flagg_gram(const flagg_view* v, const float* center, int accumulate, double* G, void* stream);
 
+/* Small cohorts (n <= 32: the reference's default 10-20 clients): D2 (device, FP64, n*n row-major,
+ * symmetric, zero diagonal) = squared pairwise distances ||x_i - x_j||^2 by DIRECT differences, as
+ * krum.py:95 forms them (torch.norm(f_i - f_j)): one pass over X, no centre vector and therefore no
+ * centre pass, no cancellation; packed fp32x2 subtract + fma per pair and column, fp32 partial sums
+ * of at most 1024 columns folded into FP64.  Non-finite rows give NaN / inf entries by IEEE
+ * arithmetic, exactly where the reference's distances are NaN / inf.  With the parameter dimension
+ * sharded, partial D2's add: all-reduce them before flagg_krum_scores_from_sqdist.
+ * `accumulate` != 0 adds into D2.  Returns FLAGG_EUNSUPPORTED for n > 32 (use flagg_gram). */
+int flagg_sqdist(const flagg_view* v, int accumulate, double* D2, void* stream);
+/* flagg_krum_scores with the squared distances of flagg_sqdist as input (D = sqrt(D2), may be NULL). */
+int flagg_krum_scores_from_sqdist(const double* D2, int n, int f, double* D, double* scores, void* stream);
+
 /* D[i,j] = sqrt(max(0, G_ii + G_jj - 2 G_ij)) (un-squared, as krum.py:95), D_ii = 0;
  * scores[i] = sum of the (n-f-2) smallest D[i,j], j != i (krum.py:122-129).
  * D may be NULL.  All device FP64.  Requires 1 <= n-f-2 <= n-1 and n <= 4096.

@@ -22,6 +22,7 @@ namespace flagg {
 
 int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st);  // gram_tc.cu
 int gram_small_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st);  // gram_small.cu (n <= 32)
+int sqdist_small_launch(flagg_view* v, int accumulate, double* D2, cudaStream_t st);                          // sqdist_small.cu (n <= 32)
 
 constexpr int GT = 64;          // output tile edge
 constexpr int GK = 32;          // columns per k-step (128 B of every row)
@@ -140,21 +141,22 @@ __device__ __forceinline__ bool krum_after(double a, double b) {   // a sorts af
     return (a > b) || (a != a && b == b);
 }
 
-template <bool FROM_D>
+// MODE 0: G is the centred Gram matrix; 1: G holds distances; 2: G holds SQUARED distances (flagg_sqdist).
+template <int MODE>
 __global__ void __launch_bounds__(256)
 krum_scores_kernel(const double* __restrict__ G, int n, int npad, int m, double* __restrict__ D,
                    double* __restrict__ scores) {
     extern __shared__ double srow[];  // [npad]
     __shared__ double red[256];
     const int i = blockIdx.x, tid = threadIdx.x;
-    const double gii = FROM_D ? 0.0 : G[size_t(i) * n + i];
+    const double gii = MODE != 0 ? 0.0 : G[size_t(i) * n + i];
     for (int j = tid; j < npad; j += blockDim.x) {
         double dv = __longlong_as_double(0x7ff8000000000000LL);  // NaN padding: sorts last, after real infinities
         if (j < n) {
-            if (FROM_D) {
+            if (MODE == 1) {
                 dv = G[size_t(i) * n + j];
             } else {
-                const double d2 = gii + G[size_t(j) * n + j] - 2.0 * G[size_t(i) * n + j];
+                const double d2 = MODE == 2 ? G[size_t(i) * n + j] : gii + G[size_t(j) * n + j] - 2.0 * G[size_t(i) * n + j];
                 dv = (j == i) ? 0.0 : ((d2 != d2) ? d2 : sqrt(fmax(d2, 0.0)));
                 if (D) D[size_t(i) * n + j] = dv;
             }
@@ -245,27 +247,44 @@ int flagg_gram(const flagg_view* cv, const float* center, int accumulate, double
     return FLAGG_OK;
 }
 
-static int krum_scores_launch(const double* G, int n, int f, double* D, double* scores, bool from_d, void* stream) {
+static int krum_scores_launch(const double* G, int n, int f, double* D, double* scores, int mode, void* stream) {
     const int m = n - f - 2;
     FLAGG_REQUIRE(n >= 1 && n <= 4096, "flagg_krum_scores: n=%d unsupported (1..4096)", n);
     FLAGG_REQUIRE(!scores || (m >= 1 && m <= n - 1), "flagg_krum_scores: need 1 <= n-f-2 <= n-1 (n=%d f=%d)", n, f);
     int npad = 2;
     while (npad < n) npad <<= 1;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (from_d) krum_scores_kernel<true><<<n, 256, sizeof(double) * npad, st>>>(G, n, npad, m, nullptr, scores);
-    else krum_scores_kernel<false><<<n, 256, sizeof(double) * npad, st>>>(G, n, npad, m, D, scores);
+    if (mode == 1) krum_scores_kernel<1><<<n, 256, sizeof(double) * npad, st>>>(G, n, npad, m, nullptr, scores);
+    else if (mode == 2) krum_scores_kernel<2><<<n, 256, sizeof(double) * npad, st>>>(G, n, npad, m, D, scores);
+    else krum_scores_kernel<0><<<n, 256, sizeof(double) * npad, st>>>(G, n, npad, m, D, scores);
     FLAGG_CUDA(cudaGetLastError());
     return FLAGG_OK;
 }
 
 int flagg_krum_scores(const double* G, int n, int f, double* D, double* scores, void* stream) {
     FLAGG_REQUIRE(G && (scores || D), "flagg_krum_scores: NULL argument");
-    return krum_scores_launch(G, n, f, D, scores, false, stream);
+    return krum_scores_launch(G, n, f, D, scores, 0, stream);
+}
+
+int flagg_sqdist(const flagg_view* cv, int accumulate, double* D2, void* stream) {
+    FLAGG_REQUIRE(cv && D2, "flagg_sqdist: NULL argument");
+    flagg_view* v = const_cast<flagg_view*>(cv);
+    v->last_stream = stream;
+    if (v->dev.n > 32) {   // GS_MAX_N
+        set_error("flagg_sqdist: serves cohorts of up to 32 clients (n=%d); larger cohorts use flagg_gram", v->dev.n);
+        return FLAGG_EUNSUPPORTED;
+    }
+    return sqdist_small_launch(v, accumulate, D2, static_cast<cudaStream_t>(stream));
+}
+
+int flagg_krum_scores_from_sqdist(const double* D2, int n, int f, double* D, double* scores, void* stream) {
+    FLAGG_REQUIRE(D2 && (scores || D), "flagg_krum_scores_from_sqdist: NULL argument");
+    return krum_scores_launch(D2, n, f, D, scores, 2, stream);
 }
 
 int flagg_krum_scores_from_distances(const double* D, int n, int f, double* scores, void* stream) {
     FLAGG_REQUIRE(D && scores, "flagg_krum_scores_from_distances: NULL argument");
-    return krum_scores_launch(D, n, f, nullptr, scores, true, stream);
+    return krum_scores_launch(D, n, f, nullptr, scores, 1, stream);
 }
 
 }  // extern "C"

@@ -370,15 +370,36 @@ def gram(u: Updates, center: Optional[torch.Tensor] = None, group=None, auto_cen
     return G
 
 
-def krum_scores(G: torch.Tensor, f: int, want_D: bool = True, want_scores: bool = True):
-    """K5.  (D [n,n] float64 ndarray or None, scores [n] float64 ndarray or None)."""
+def krum_scores(G: torch.Tensor, f: int, want_D: bool = True, want_scores: bool = True, squared: bool = False):
+    """K5.  (D [n,n] float64 ndarray or None, scores [n] float64 ndarray or None).  ``G``: the centred
+    Gram matrix, or with ``squared`` the squared distances of ``sqdist``."""
     n = G.shape[0]
     with torch.cuda.device(G.device):
         scores = torch.empty(n, dtype=torch.float64, device=G.device) if want_scores else None
         D = torch.empty((n, n), dtype=torch.float64, device=G.device) if want_D else None
-        check(lib().flagg_krum_scores(G.data_ptr(), n, f, D.data_ptr() if want_D else None,
-                                      scores.data_ptr() if want_scores else None, _stream()), "flagg_krum_scores")
+        fn, name = (lib().flagg_krum_scores_from_sqdist, "flagg_krum_scores_from_sqdist") if squared else \
+            (lib().flagg_krum_scores, "flagg_krum_scores")
+        check(fn(G.data_ptr(), n, f, D.data_ptr() if want_D else None,
+                 scores.data_ptr() if want_scores else None, _stream()), name)
         return (D.cpu().numpy() if want_D else None), (scores.cpu().numpy() if want_scores else None)
+
+
+SMALL_COHORT = 32   # up to here distances come from direct differences (flagg_sqdist): one read of X, no centre
+
+
+def sqdist(u: Updates, group=None) -> torch.Tensor:
+    """K4, small cohorts.  FP64 squared pairwise distances [n, n] on the device by direct differences
+    (krum.py:95 subtracts first too); all-reduced over ``group`` when the parameter dimension is sharded
+    (partial squared distances add)."""
+    u = u.resident()
+    if u.n > SMALL_COHORT:
+        raise FlaggError(f"sqdist serves cohorts of up to {SMALL_COHORT} clients; larger ones use gram()")
+    with torch.cuda.device(u.device):
+        D2 = torch.empty((u.n, u.n), dtype=torch.float64, device=u.device)
+        check(lib().flagg_sqdist(u.view(), 0, D2.data_ptr(), _stream()), "flagg_sqdist")
+        if group is not None:
+            all_reduce(D2, group, "sum")
+    return D2
 
 
 def krum_distances_scores(u: Updates, f: int, group=None, want_D: bool = True):
@@ -386,6 +407,9 @@ def krum_distances_scores(u: Updates, f: int, group=None, want_D: bool = True):
     K5.  A cohort with a non-finite row (a client that sent NaN / Inf) takes the exact path
     below, so that client is ranked last as in the reference instead of poisoning the centre."""
     u = u.resident()
+    if u.n <= SMALL_COHORT:
+        # direct differences: NaN / Inf rows give NaN / inf distances by IEEE arithmetic, as torch.norm(f_i - f_j) does
+        return krum_scores(sqdist(u, group=group), f, want_D, squared=True)
     G = gram(u, group=group)
     D, scores = krum_scores(G, f, want_D)
     if np.all(np.isfinite(scores)):

@@ -37,7 +37,7 @@ class KrumDefense(BaseDefense):
         if n >= 3:      # scores with one neighbour come for free and route non-finite rows to the exact path
             D, _ = engine.krum_distances_scores(u, n - 3, group=self._group, want_D=True)
         else:
-            D, _ = engine.krum_scores(engine.gram(u, group=self._group), 0, want_D=True, want_scores=False)
+            D, _ = engine.krum_scores(engine.sqdist(u, group=self._group), 0, want_D=True, want_scores=False, squared=True)
         u.close()
         return D
 

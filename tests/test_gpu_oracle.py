@@ -149,7 +149,9 @@ def test_gather_map_needs_512_byte_alignment_else_ldg():
     rng = np.random.RandomState(77)
     n, d = 20, 1000
     X = rows_model(rng, n, d)
-    ups = [[torch.zeros(d + 4, device="cuda")[4:].copy_(torch.from_numpy(X[i]))] for i in range(n)]
+    # allocations of different sizes: the rows are not equally spaced (that would be a dense matrix: 2-D TMA boxes)
+    ups = [[torch.zeros(d + 4 + 1024 * (i % 3), device="cuda")[4:4 + d].copy_(torch.from_numpy(X[i]))] for i in range(n)]
+    assert len({ups[i + 1][0].data_ptr() - ups[i][0].data_ptr() for i in range(n - 1)}) > 1
     u = engine.Updates(ups)
     assert np.array_equal(bits(engine.colwise_select(u, MEDIAN).cpu().numpy()), bits(oracle64.median_stable(X)))
     os.environ["FLAGG_K1_IMPL"] = "bulk"
@@ -369,6 +371,74 @@ def test_gram_small_cohorts_vs_fp64(n, seg, f, impl, monkeypatch):
         s64 = oracle64.krum_scores64(D64, f)
         np.testing.assert_allclose(scores, s64, rtol=1e-5)
         assert int(np.argmin(scores)) == int(np.argmin(s64))
+    u.close()
+
+
+@pytest.mark.parametrize("aligned", [True, False])
+@pytest.mark.parametrize("n,seg,f", [(2, [300], 0), (3, [4096], 0), (4, [4096], 0), (8, [777, 33], 2), (9, [5000, 1, 260], 2),
+                                     (10, [288, 32, 18432, 64, 401408, 128, 1280, 10], 2), (16, [3000], 4), (17, [64, 2050], 4),
+                                     (20, [130000, 36], 5), (24, [50000], 6), (25, [4100, 95], 6), (31, [700, 3], 8), (32, [9000, 31], 8)])
+def test_sqdist_small_cohorts_vs_fp64(n, seg, f, aligned):
+    """flagg_sqdist (the reference's default cohort sizes, n <= 32): squared distances by direct
+    differences with packed fp32x2 arithmetic, every job layout (1 / 2 / 3 / 4 row blocks), 128-bit
+    and 4-byte copies, ragged tensors.  Distances within 1e-5 of FP64 (measured ~1e-7), exact
+    symmetry and zero diagonal, exactly 0 between duplicate rows, Krum ranking as FP64's, repeatable
+    bit for bit, accumulate=1 adds."""
+    from flagg import engine
+    from flagg._lib import check, lib
+    d = sum(seg)
+    rng = np.random.RandomState(n + d)
+    X = rows_model(rng, n, d, byz=f)
+    if n > 2:
+        X[1] = X[0]
+    if aligned:
+        ups = dev_lists(X, seg)
+    else:                                                              # 4-byte aligned views into one buffer
+        big = torch.zeros((n, d + 1), device="cuda")
+        big[:, 1:] = torch.from_numpy(X).cuda()
+        offs = np.concatenate([[0], np.cumsum(seg)]).astype(int)
+        ups = [[big[i, 1 + offs[p]:1 + offs[p + 1]] for p in range(len(seg))] for i in range(n)]
+    u = engine.Updates(ups)
+    D2 = engine.sqdist(u)
+    D, scores = engine.krum_scores(D2, f, want_scores=n - f - 2 >= 1, squared=True)
+    D64 = oracle64.distances64(X)
+    assert np.all(np.diag(D) == 0) and np.array_equal(D, D.T)
+    assert n == 2 or D[0, 1] == 0.0
+    mask = D64 > 0
+    err = np.max(np.abs(D[mask] - D64[mask]) / D64[mask])
+    assert err <= 1e-5, err
+    assert err <= 2e-6                                                 # no cancellation: an fp32 sum of at most 1024 squares per lane
+    if n - f - 2 >= 1:
+        s64 = oracle64.krum_scores64(D64, f)
+        np.testing.assert_allclose(scores, s64, rtol=1e-5)
+        assert int(np.argmin(scores)) == int(np.argmin(s64))
+    again = engine.sqdist(u)
+    assert torch.equal(D2, again)
+    check(lib().flagg_sqdist(u.view(), 1, again.data_ptr(), torch.cuda.current_stream().cuda_stream), "flagg_sqdist")
+    assert torch.equal(again, 2.0 * D2)
+    u.close()
+
+
+def test_sqdist_nonfinite_rows_follow_ieee_like_torch_norm():
+    """A NaN client, an Inf client and a pair of Inf clients: flagg_sqdist gives NaN / inf exactly
+    where the reference's torch.norm(f_i - f_j) does (krum.py:95), no special path involved."""
+    from flagg import engine
+    rng = np.random.RandomState(3)
+    n, d = 14, 3000
+    X = rows_model(rng, n, d)
+    X[2, 17] = np.nan
+    X[5, 100] = np.inf
+    X[9, 100] = np.inf                                                # inf - inf = NaN between rows 5 and 9
+    X[11, 2999] = -np.inf
+    u = engine.Updates(dev_lists(X, [1000, 2000]))
+    D, _ = engine.krum_scores(engine.sqdist(u), 3, squared=True)
+    with np.errstate(all="ignore"):
+        ref = ref_port.krum_distances(torch.from_numpy(X))
+    assert np.array_equal(np.isnan(D), np.isnan(ref)) and np.array_equal(np.isinf(D), np.isinf(ref))
+    fin = np.isfinite(ref) & (ref > 0)
+    assert np.max(np.abs(D[fin] - ref[fin]) / ref[fin]) <= 1e-5
+    with pytest.raises(engine.FlaggError):
+        engine.sqdist(engine.Updates(dev_lists(rows_model(rng, 33, 64), [64])))
     u.close()
 
 
