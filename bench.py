@@ -443,25 +443,51 @@ def c2_defenses(dist_on, with_cpu):
     return out
 
 
-def _alone_on_rank0(rank, dist_on, fn):
-    """Run ``fn`` on rank 0 only (the other ranks wait): the N = 1 point of a strong-scaling pair,
-    measured in the same job so the line can carry its own efficiency."""
+def _bcast(val, dist_on):
+    """rank 0's value on every rank."""
     import torch.distributed as dist
-    val = fn() if rank == 0 else None
-    torch.cuda.synchronize()
     if dist_on:
-        dist.barrier()
         box = [val]
         dist.broadcast_object_list(box, src=0)
-        val = box[0]
+        return box[0]
     return val
 
 
-def strong_scaling(rank, world, dist_on, comm, steps, with_cpu):
-    """BASELINE configs 4 and 5 as strong scaling: the SAME round column-sharded over the N ranks
-    (flagg.sharding.shard_bounds), timed through the plugin classes with ``process_group=comm``."""
-    from flagg import engine
+def _ingest(make_rows, n, d, rank, world, dist_on, comm):
+    """The round's update matrix as the sharded path meets it: ONE matrix, generated on rank 0 (the process
+    that received the clients' updates), column-sharded over the ranks by flagg_comm_scatter_columns
+    (ncclSend / ncclRecv per row and peer over NVLink).  Returns (this rank's shard as update lists, rank 0's
+    full lists or None, (lo, hi), scatter seconds or None)."""
+    import torch.distributed as dist
     from flagg.sharding import shard_bounds
+    torch.cuda.empty_cache()
+    full = None
+    if rank == 0:
+        X = make_rows()
+        full = [[X[i]] for i in range(n)]
+    if world == 1:
+        return full, full, (0, d), None
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    mine, (lo, hi) = comm.scatter_columns(full, n, [d], root=0)      # the root keeps views of its own rows
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / 1e3], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    assert (lo, hi) == shard_bounds(d, world)[rank]
+    return mine, full, (lo, hi), float(t.item())
+
+
+def strong_scaling(rank, world, dist_on, comm, steps, with_cpu):
+    """BASELINE configs 4 and 5 as strong scaling: the SAME round -- one matrix generated on rank 0 and
+    column-sharded over the N ranks (ingest, reported, outside the timed aggregation) -- timed through the
+    plugin classes with ``process_group=comm``; at N > 1 rank 0 then runs the whole round alone on the same
+    matrix, which gives the line its own N = 1 time (efficiency = t1 / (N t_N)) and checks that the sharded
+    run selected exactly what the unsharded one selects."""
+    import torch.distributed as dist
+    from flagg import engine
     from src.defenses import FLTrustDefense, GradientClippingDefense, MultiKrumDefense
 
     class Fixed(FLTrustDefense):                 # g0 injected: the root-dataset SGD step is training, not aggregation
@@ -474,22 +500,18 @@ def strong_scaling(rank, world, dist_on, comm, steps, with_cpu):
     # ---------------- C4: 1000 x 25,000,000, Multi-Krum f = 100, multi_k = 900 ----------------
     n, d, f, mk = 1000, 25_000_000, 100, 900
     ne = [1] * n
-
-    def c4_time(cols, group, k, w, seed):
-        torch.cuda.empty_cache()
-        X = synth_rows(n, cols, f, seed, spread=0.3)
-        ups = [[X[i]] for i in range(n)]
-        defense = MultiKrumDefense({"num_malicious": f, "multi_k": mk, "process_group": group})
-        t = time_steps(lambda: defense.aggregate(ups, ne), k, w, dist_on and group is not None) / k
-        u = engine.Updates(ups)
-        tg = time_steps(lambda: engine.gram(u), 3, 1, False) / 3          # centre + local Gram kernel, no collective
-        u.close()
-        sel_ok = set(defense.rejected_clients[-f:]) == set(range(f))
-        del X, ups, u
-        return t, tg, sel_ok
-
-    lo, hi = shard_bounds(d, world)[rank]
-    t, tg, sel_ok = c4_time(hi - lo, comm, steps, 3, 31 + rank)
+    mine, full, (lo, hi), t_scatter = _ingest(lambda: synth_rows(n, d, f, 31, spread=0.3), n, d, rank, world, dist_on, comm)
+    defense = MultiKrumDefense({"num_malicious": f, "multi_k": mk, "process_group": comm})
+    t = time_steps(lambda: defense.aggregate(mine, ne), steps, 3, dist_on) / steps
+    u = engine.Updates(mine)
+    tg = time_steps(lambda: engine.gram(u), 3, 1, False) / 3          # centre + this rank's Gram kernel, no collective
+    u.close()
+    del u
+    tg_t = torch.tensor([tg], dtype=torch.float64, device="cuda")
+    if dist_on:
+        dist.all_reduce(tg_t, op=dist.ReduceOp.MAX)
+        tg = float(tg_t.item())
+    sel_ok = set(defense.rejected_clients[-f:]) == set(range(f))
     ar_us = None
     if comm is not None:
         G = torch.zeros((n, n), dtype=torch.float64, device="cuda")
@@ -511,11 +533,25 @@ def strong_scaling(rank, world, dist_on, comm, steps, with_cpu):
                        "frac_vs_bf16_over_6": (flops / tg / 1e12 / (bf16_burst / 6)) if bf16_burst else None,
                        "tf32_dense_measured_burst": tf32_burst, "tf32_dense_measured_sustained": tf32_sust}}
     if world > 1:
-        t1 = _alone_on_rank0(rank, dist_on, lambda: c4_time(d, None, 5, 2, 31)[0])
+        c4["ingest_scatter"] = {"ms": t_scatter * 1e3, "GBps": 4.0 * n * (d - d // world) / t_scatter / 1e9,
+                                "what": "rank 0 -> peers, [n, d/N] column shards, ncclSend/ncclRecv per (row, peer) over NVLink; outside the timed round"}
+        sel = list(defense.selected_clients)
+        del mine
+        res = None
+        if rank == 0:
+            alone = MultiKrumDefense({"num_malicious": f, "multi_k": mk})
+            t1 = time_steps(lambda: alone.aggregate(full, ne), 5, 2, False) / 5
+            res = (t1, alone.selected_clients == sel)
+        torch.cuda.synchronize()
+        dist.barrier()
+        t1, same_sel = _bcast(res, dist_on)
         c4["t1_ms_rank0_alone"] = t1 * 1e3
         c4["efficiency"] = t1 / (world * t)
+        c4["selection_identical_to_unsharded"] = bool(same_sel)
     else:
         c4["efficiency"] = 1.0
+        del mine
+    del full
     if with_cpu:
         c4["cpu_baseline"] = cpu_krum_extrapolated(n, d)
     out["c4"] = c4
@@ -524,24 +560,24 @@ def strong_scaling(rank, world, dist_on, comm, steps, with_cpu):
     ne = [50 + (i % 7) for i in range(n)]
     g0_full = torch.randn(d, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5)) * 1e-3
 
-    def c5_time(cols_lo, cols_hi, group, k, w, seed):
-        torch.cuda.empty_cache()
-        X = synth_rows(n, cols_hi - cols_lo, n // 10, seed, theta_sigma=0.0, spread=0.3)
-        X[n // 10:] += 0.7 * g0_full[cols_lo:cols_hi]
-        ups = [[X[i]] for i in range(n)]
-        g0 = [g0_full] if group is not None else [g0_full[cols_lo:cols_hi]]
-        on = dist_on and group is not None
+    def make_c5():
+        X = synth_rows(n, d, n // 10, 51, theta_sigma=0.0, spread=0.3)
+        X[n // 10:] += 0.7 * g0_full
+        return X
+
+    def c5_round(ups, group, k, w, on):
         fl = Fixed({"process_group": group})
-        tf = time_steps(lambda: fl.aggregate(ups, ne, global_params=g0), k, w, on) / k
-        clip = float(np.median(np.sqrt(engine.row_stats(engine.Updates(ups), group=group)["sumsq"])))
+        tf = time_steps(lambda: fl.aggregate(ups, ne, global_params=[g0_full]), k, w, on) / k
+        uu = engine.Updates(ups)
+        clip = float(np.median(np.sqrt(engine.row_stats(uu, group=group)["sumsq"])))
+        uu.close()
         gc = GradientClippingDefense({"clip_norm": clip, "clip_type": "l2", "process_group": group})
         tc = time_steps(lambda: gc.aggregate(ups, ne), k, w, on) / k
         ok = bool(np.all(np.array(fl.trust_scores[n // 10:]) > 0.1)) and 0 < gc.clipped_count < n
-        del X, ups
-        return tf, tc, ok
+        return tf, tc, ok, (fl.detect_malicious(None, None), gc.clipped_count)
 
-    lo, hi = shard_bounds(d, world)[rank]
-    tf, tc, ok = c5_time(lo, hi, comm, steps, 3, 51 + rank)
+    mine, full, (lo, hi), t_scatter = _ingest(make_c5, n, d, rank, world, dist_on, comm)
+    tf, tc, ok, det = c5_round(mine, comm, steps, 3, dist_on)
     alg = 4.0 * (hi - lo) * (2 * n + 2)
     c5 = {"workload": "C5: 500 clients x 11,689,512 params, FLTrust (injected g0) and GradientClipping L2, one round each",
           "n_gpus": world, "cols_per_gpu": hi - lo, "steps": steps, "sane": ok,
@@ -551,13 +587,24 @@ def strong_scaling(rank, world, dist_on, comm, steps, with_cpu):
                                 "GBps": 4.0 * n * d / tc / 1e9, "roofline_frac_hbm": 4.0 * (hi - lo) * (2 * n + 1) / tc / 1e9 / hbm},
           "algorithmic_bytes_per_gpu": alg}
     if world > 1:
-        t1 = _alone_on_rank0(rank, dist_on, lambda: c5_time(0, d, None, 5, 2, 51)[:2])
-        c5["fltrust"]["t1_ms_rank0_alone"], c5["gradient_clipping"]["t1_ms_rank0_alone"] = t1[0] * 1e3, t1[1] * 1e3
-        c5["fltrust"]["efficiency"] = t1[0] / (world * tf)
-        c5["gradient_clipping"]["efficiency"] = t1[1] / (world * tc)
+        c5["ingest_scatter"] = {"ms": t_scatter * 1e3, "GBps": 4.0 * n * (d - d // world) / t_scatter / 1e9}
+        del mine
+        res = None
+        if rank == 0:
+            t1f, t1c, _, det1 = c5_round(full, None, 5, 2, False)
+            res = (t1f, t1c, det1 == det)
+        torch.cuda.synchronize()
+        dist.barrier()
+        t1f, t1c, same_det = _bcast(res, dist_on)
+        c5["fltrust"]["t1_ms_rank0_alone"], c5["gradient_clipping"]["t1_ms_rank0_alone"] = t1f * 1e3, t1c * 1e3
+        c5["fltrust"]["efficiency"] = t1f / (world * tf)
+        c5["gradient_clipping"]["efficiency"] = t1c / (world * tc)
         c5["efficiency"] = c5["fltrust"]["efficiency"]
+        c5["detections_identical_to_unsharded"] = bool(same_det)
     else:
         c5["efficiency"] = 1.0
+        del mine
+    del full
     if with_cpu:
         c5["cpu_baseline"] = cpu_fltrust_sample(n, d, 1_000_000)
     del g0_full

@@ -227,6 +227,15 @@ int flagg_comm_size(const flagg_comm* c);
 int flagg_comm_rank(const flagg_comm* c);
 int flagg_allreduce_f64(flagg_comm* c, double* buf, size_t count, int op, void* stream);
 int flagg_allreduce_f32(flagg_comm* c, float* buf, size_t count, int op, void* stream);
+/* Ingest (robust_server.py:99-108 hands the server ONE process's list of whole client updates): rank
+ * `root` holds n rows x P tensors on its device (root_seg_ptrs: HOST array [n*P] of DEVICE addresses,
+ * NULL elsewhere); rank r receives columns [lo[r], hi[r]) of every row (flattened-vector coordinates,
+ * host arrays [nranks], identical on all ranks) as one dense device matrix dst[n, ld].  ncclSend /
+ * ncclRecv per (row, peer, tensor piece) over NVLink, stream ordered; the root's own shard is copied
+ * device-to-device when dst != NULL (NULL: the root keeps using views of its rows). */
+int flagg_comm_scatter_columns(flagg_comm* c, int root, int n, int P, const int64_t* seg_numel,
+                               const void* const* root_seg_ptrs, const int64_t* lo, const int64_t* hi,
+                               float* dst, int64_t ld, void* stream);
 
 #ifdef __cplusplus
 }

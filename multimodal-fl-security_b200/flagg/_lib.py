@@ -61,6 +61,7 @@ def lib():
         "flagg_comm_rank": (i32, [vp]),
         "flagg_allreduce_f64": (i32, [vp, vp, C.c_size_t, i32, vp]),
         "flagg_allreduce_f32": (i32, [vp, vp, C.c_size_t, i32, vp]),
+        "flagg_comm_scatter_columns": (i32, [vp, i32, i32, i32, C.POINTER(i64), C.POINTER(vp), C.POINTER(i64), C.POINTER(i64), vp, i64, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)          # AttributeError here = header/library mismatch
@@ -74,7 +75,7 @@ EXPORTS = ["flagg_version", "flagg_last_error", "flagg_device_info", "flagg_view
            "flagg_sqdist", "flagg_krum_scores_from_sqdist", "flagg_view_cols", "flagg_view_rows", "flagg_colwise_select", "flagg_row_reduce", "flagg_row_combine",
            "flagg_gram", "flagg_krum_scores", "flagg_colwise_select_host", "flagg_upload_rows", "flagg_host_release", "flagg_comm_unique_id",
            "flagg_comm_create", "flagg_comm_destroy", "flagg_comm_size", "flagg_comm_rank", "flagg_allreduce_f64",
-           "flagg_allreduce_f32"]
+           "flagg_allreduce_f32", "flagg_comm_scatter_columns"]
 
 
 def check(rc: int, what: str) -> None:

@@ -65,6 +65,39 @@ class Comm:
             raise ValueError(f"all_reduce: unsupported dtype {t.dtype}")
         return t
 
+    def scatter_columns(self, client_updates, n: int, numel: Sequence[int], root: int = 0, copy_root: bool = False):
+        """Ingest for the sharded path: rank ``root`` holds the whole client updates on its device
+        (``client_updates``: List[List[Tensor]]; ignored elsewhere), every rank gets its column shard
+        (flagg.sharding.shard_bounds) of every client.  ``n`` clients, ``numel``: elements of each of the P
+        tensors (known to every rank -- the model's shapes).  Returns (updates, (lo, hi)) where ``updates``
+        is a list of n one-tensor lists over a dense [n, hi - lo] device matrix (on the root: zero-copy
+        views of its own rows unless ``copy_root``).  flagg_comm_scatter_columns: ncclSend / ncclRecv per
+        (row, peer) over NVLink, enqueued on the current stream."""
+        from .sharding import shard_bounds, shard_update_lists
+        numel = [int(x) for x in numel]
+        P, d = len(numel), int(sum(numel))
+        bounds = shard_bounds(d, self.nranks)
+        lo, hi = bounds[self.rank]
+        los = (C.c_int64 * self.nranks)(*[b[0] for b in bounds])
+        his = (C.c_int64 * self.nranks)(*[b[1] for b in bounds])
+        seg = (C.c_int64 * P)(*numel)
+        ptrs, keep, dst = None, None, None
+        if self.rank == root:
+            u = Updates(client_updates)
+            if u.on_host or u.n != n or u.numel != numel:
+                raise ValueError("scatter_columns: the root's updates must be device tensors of the announced shapes")
+            _, ptrs = u._ptr_tables()
+            keep = u
+        if self.rank != root or copy_root:
+            dst = torch.empty((n, max(hi - lo, 1)), dtype=torch.float32, device="cuda")
+        check(lib().flagg_comm_scatter_columns(self._h, int(root), int(n), P, seg, ptrs, los, his,
+                                               dst.data_ptr() if dst is not None else None, max(hi - lo, 1), _stream()),
+              "flagg_comm_scatter_columns")
+        if dst is not None:
+            return [[dst[i, :hi - lo]] for i in range(n)], (lo, hi)
+        mine, _ = shard_update_lists(keep.rows, self.rank, self.nranks)
+        return mine, (lo, hi)
+
     def close(self) -> None:
         if getattr(self, "_h", None):
             lib().flagg_comm_destroy(self._h)

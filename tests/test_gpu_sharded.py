@@ -132,6 +132,20 @@ def _worker(rank, world, port, errq):
         for cls, cfg in ((MedianDefense, {}), (TrimmedMeanDefense, {"trim_ratio": 0.2})):
             a, full, b, part, (lo, hi) = both(cls, cfg, ups, [1] * n)
             assert same_bits(part, full[lo:hi])
+        # ---- ingest: rank 0 holds the whole cohort, every rank receives its column shard over NCCL ----
+        n, seg, f = 40, [50_000, 1234, 30_000, 7], 5
+        X = _rows(n, seg, f, 21)
+        ups = _lists(X, seg) if rank == 0 else None
+        for copy_root in (False, True):
+            mine, (lo, hi) = comm.scatter_columns(ups, n, seg, root=0, copy_root=copy_root)
+            got = torch.stack([torch.cat([t.reshape(-1) for t in row]) for row in mine]).cpu().numpy()
+            assert np.array_equal(got.view(np.uint32), X[:, lo:hi].view(np.uint32)), "scattered shard differs from the root's columns"
+            b = MultiKrumDefense({"num_malicious": f, "multi_k": 20, "process_group": comm})
+            part = _flat(b.aggregate(mine, [1] * n))
+            if rank == 0:
+                a = MultiKrumDefense({"num_malicious": f, "multi_k": 20})
+                full = _flat(a.aggregate(ups, [1] * n))
+                assert a.selected_clients == b.selected_clients and same_bits(part, full[lo:hi])
         torch.cuda.synchronize()
         dist.barrier()
         comm.close()
