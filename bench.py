@@ -467,6 +467,9 @@ def _ingest(make_rows, n, d, rank, world, dist_on, comm):
         full = [[X[i]] for i in range(n)]
     if world == 1:
         return full, full, (0, d), None
+    # NCCL builds its point-to-point connections on first use (~0.6 s): a small scatter first, then the timed one
+    w = torch.zeros((8, 4096 * world), device="cuda")
+    comm.scatter_columns([[w[i]] for i in range(8)] if rank == 0 else None, 8, [4096 * world], root=0)
     torch.cuda.synchronize()
     dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -10,6 +10,7 @@
 // that copy) or from the loader path, so libflagg.so has no link-time dependency on it and the
 // single-GPU path never touches it.
 #include <dlfcn.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -184,20 +185,26 @@ int flagg_comm_scatter_columns(flagg_comm* c, int root, int n, int P, const int6
         }
         return FLAGG_OK;
     };
-    for (int i0 = 0; i0 < n; i0 += SC_GROUP_ROWS) {
-        const int i1 = std::min(n, i0 + SC_GROUP_ROWS);
+    int group_rows = SC_GROUP_ROWS;
+    if (const char* e = getenv("FLAGG_SCATTER_GROUP_ROWS")) group_rows = std::max(1, atoi(e));
+    for (int i0 = 0; i0 < n; i0 += group_rows) {
+        const int i1 = std::min(n, i0 + group_rows);
         FLAGG_NCCL(nccl().GroupStart());
         int rc = FLAGG_OK;
-        for (int i = i0; i < i1 && rc == FLAGG_OK; ++i) {
-            if (is_root) {
-                for (int r = 0; r < c->nranks && rc == FLAGG_OK; ++r) {
-                    if (r == root) continue;
+        if (is_root) {      // peer-major inside a group: each peer's operations are consecutive, in row order
+            for (int r = 0; r < c->nranks && rc == FLAGG_OK; ++r) {
+                if (r == root) continue;
+                for (int i = i0; i < i1 && rc == FLAGG_OK; ++i)
                     rc = for_pieces(lo[r], hi[r], [&](int p, int64_t off, int64_t len, int64_t) -> int {
                         const float* src = static_cast<const float*>(root_seg_ptrs[size_t(i) * P + p]) + off;
                         FLAGG_NCCL(nccl().Send(src, size_t(len), ncclFloat32, r, c->comm, st));
                         return FLAGG_OK;
                     });
-                }
+            }
+        }
+        for (int i = i0; i < i1 && rc == FLAGG_OK; ++i) {
+            if (is_root) {
+                break;
             } else {
                 rc = for_pieces(lo[c->rank], hi[c->rank], [&](int, int64_t, int64_t len, int64_t at) -> int {
                     FLAGG_NCCL(nccl().Recv(dst + int64_t(i) * ld + at, size_t(len), ncclFloat32, root, c->comm, st));
