@@ -132,13 +132,31 @@ int flagg_row_combine(const flagg_view* v, int m, const int32_t* rows, const flo
                       const float* w2, float divisor, float* out, void* stream);
 
 /* Same combination with every operand resident on the DEVICE (no host round trip between the
- * reductions that produce the weights and this pass): d_rows [m] int32 or NULL, d_w1 / d_w2 [m]
+ * reductions that produce the weights and this pass): d_rows [m] int32 or NULL (negative entries are skipped), d_w1 / d_w2 [m]
  * fp32 or NULL (= 1.0f), d_divisor one fp32.  With `prev` (device fp32 [d]) and `delta_sumsq`
  * (device, one double) it also returns ||out - prev||^2 (fp32 differences and squares, FP64 sum
  * in a fixed order): the Weiszfeld stopping rule torch.norm(new - current) at trimmed_mean.py:255. */
 int flagg_row_combine_dev(const flagg_view* v, int m, const int32_t* d_rows, const float* d_w1,
                           const float* d_w2, const float* d_divisor, float* out, const float* prev,
                           double* delta_sumsq, void* stream);
+
+/* Per-round weights on the device: the reference's Python arithmetic on the flagg_row_reduce statistics, so that
+ * a clipping / trust round is K2 -> (all-reduce) -> this -> flagg_row_combine_dev with no host round trip.
+ *   FLAGG_W_FLTRUST    trust_i = max(0, fp32 dot_i / (||x_i|| ||g0||)), scale_i = ||g0|| / ||x_i||  (fltrust.py:170-186,
+ *                      205-216); divisor = fp32(sum trust, Python order); counts[1] = 1 when sum trust < 1e-10 (:258-260)
+ *   FLAGG_W_CLIP       scale_i = fp32(p0 / norm_i) if norm_i > p0 (differential_privacy.py:242-245; norms: L2 from
+ *                      sumsq, or Linf when sumsq == NULL and linf is given); counts[1] = clients clipped
+ *   FLAGG_W_DPSGD      scale_i = (1 / norm_i) * fp32(p0) in fp32 if norm_i > fp32(p0) (:90-92)
+ *   FLAGG_W_NORMBOUND  keep client i iff p1 <= norm_i <= p0 (:313); all rejected -> all kept, counts[1] = 1 (:319-322)
+ * num_examples: device FP64 [n] holding the integer counts (w2 = fp32(count) for the non-FLTrust rules; divisor =
+ * fp32 of their exact sum over the kept clients, as Python's int sum gives it).
+ * Outputs (device): rows [n] int32 = kept clients in order, then -1 (flagg_row_combine_dev skips negative entries:
+ * pass m = n); w1, w2 [n] fp32 aligned with rows; divisor [1] fp32; info [n] FP64 (trust score / norm per client);
+ * counts [2] int32 (kept, flag); scratch: n bytes. */
+typedef enum flagg_weight_rule { FLAGG_W_FLTRUST = 0, FLAGG_W_CLIP = 1, FLAGG_W_DPSGD = 2, FLAGG_W_NORMBOUND = 3 } flagg_weight_rule;
+int flagg_round_weights(int rule, int n, const double* sumsq, const double* dot, const double* g0_sumsq, const float* linf,
+                        const double* num_examples, double p0, double p1, int32_t* rows, float* w1, float* w2, float* divisor,
+                        double* info, int32_t* counts, void* scratch_n_bytes, void* stream);
 
 /* Weiszfeld weights on the device (trimmed_mean.py:245-251): dist_i = max(fp32 sqrt(sumsq_i), 1e-10),
  * w_i = 1 / dist_i, *wsum = sum_i w_i (FP64 sum rounded once).  sumsq: device FP64 [n] (the centred

@@ -190,11 +190,13 @@ row_combine_kernel(ViewDev v, int m, const int* __restrict__ rows, const float* 
     for (int j0 = 0; j0 < m; j0 += RC_UNROLL) {
         float x[RC_UNROLL][4];
         float a1[RC_UNROLL], a2[RC_UNROLL];
+        int ri[RC_UNROLL];
 #pragma unroll
         for (int jj = 0; jj < RC_UNROLL; ++jj) {
             const int j = j0 + jj;
-            if (j < m) {
-                const float* row = v.seg_ptrs[size_t(rows ? __ldg(rows + j) : j) * v.P + p] + c0;
+            ri[jj] = (j < m) ? (rows ? __ldg(rows + j) : j) : -1;      // a negative entry is skipped (device-side compaction pads with -1)
+            if (ri[jj] >= 0) {
+                const float* row = v.seg_ptrs[size_t(ri[jj]) * v.P + p] + c0;
                 a1[jj] = w1 ? __ldg(w1 + j) : 1.0f;
                 a2[jj] = w2 ? __ldg(w2 + j) : 1.0f;
                 if (vec) {
@@ -208,7 +210,7 @@ row_combine_kernel(ViewDev v, int m, const int* __restrict__ rows, const float* 
         }
 #pragma unroll
         for (int jj = 0; jj < RC_UNROLL; ++jj) {
-            if (j0 + jj < m) {
+            if (ri[jj] >= 0) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
                     acc[q] = __fadd_rn(acc[q], __fmul_rn(a2[jj], __fmul_rn(a1[jj], x[jj][q])));
@@ -280,11 +282,101 @@ __global__ void __launch_bounds__(32) weiszfeld_weights_kernel(const double* __r
     if (threadIdx.x == 0) *wsum = float(s);
 }
 
+// Per-round weights on the device (no host round trip between K2 and K3): the fp32 / double arithmetic of the
+// reference's Python, operation for operation, on the K2 statistics.  One CTA: thread i forms client i's terms,
+// thread 0 then walks the clients in order for the double-precision running sums Python's sum() forms and for the
+// order-preserving compaction of the rows K3 has to read (the rest of `rows` is filled with -1 = skip).
+//   info[i]  : FLTRUST trust score (fltrust.py:186), otherwise the client's norm (differential_privacy.py:227-232)
+//   counts[0]: rows kept (m)   counts[1]: FLTRUST: 1 if sum(trust) < 1e-10 (:258-260, caller returns g0);
+//              CLIP / DPSGD: clients clipped;  NORMBOUND: 1 if every client was rejected (:319-322, all are used)
+__global__ void __launch_bounds__(256)
+round_weights_kernel(int rule, int n, const double* __restrict__ sumsq, const double* __restrict__ dot,
+                     const double* __restrict__ g0_sumsq, const float* __restrict__ linf, const double* __restrict__ num_examples,
+                     double p0, double p1, int use_linf, int* __restrict__ rows, float* __restrict__ w1, float* __restrict__ w2,
+                     float* __restrict__ divisor, double* __restrict__ info, int* __restrict__ counts, unsigned char* __restrict__ keep) {
+    const float nanf_ = __int_as_float(0x7fc00000);
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const double ss = sumsq ? sumsq[i] : 0.0;
+        const float norm32 = use_linf ? linf[i] : ((ss != ss) ? nanf_ : float(sqrt(ss)));   // torch.norm / max|x| as an fp32 value
+        const double norm = double(norm32);
+        float a1 = 1.0f, a2 = num_examples ? float(num_examples[i]) : 1.0f;
+        unsigned char k = 1;
+        double inf = norm;
+        if (rule == FLAGG_W_FLTRUST) {
+            const float sn = float(sqrt(*g0_sumsq));
+            const bool tiny = norm32 < 1e-10f;
+            const float q = __fdiv_rn(float(dot[i]), __fmul_rn(norm32, sn));
+            const float trust = (!tiny && sn >= 1e-10f && q > 0.f) ? q : 0.f;          // max(0.0, q): NaN -> 0.0
+            a1 = tiny ? 1.0f : __fdiv_rn(sn, norm32);                                  // fltrust.py:208-214
+            a2 = trust;
+            inf = double(trust);
+            // a zero-trust row adds +-0 to a sum that starts at +0: skipped unless it holds Inf / NaN (0 * Inf = NaN)
+            k = (trust != 0.f || !(fabs(ss) <= 1.79769313486231570e308)) ? 1 : 0;
+        } else if (rule == FLAGG_W_CLIP) {
+            if (norm > p0) a1 = float(p0 / norm);                                      // Python float division, then fp32
+        } else if (rule == FLAGG_W_DPSGD) {
+            const float clip32 = float(p0);
+            if (norm32 > clip32) a1 = __fmul_rn(__fdiv_rn(1.0f, norm32), clip32);      // norm.reciprocal() * clip
+        } else {
+            k = (p1 <= norm && norm <= p0) ? 1 : 0;                                    // min_norm <= norm <= max_norm
+        }
+        w1[i] = a1;
+        w2[i] = a2;
+        info[i] = inf;
+        keep[i] = k;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int m = 0, flag = 0;
+        double total = 0.0;
+        if (rule == FLAGG_W_FLTRUST) {
+            for (int i = 0; i < n; ++i) total += info[i];                              // Python sum(): left to right, double
+            flag = (total < 1e-10) ? 1 : 0;
+        } else if (rule == FLAGG_W_NORMBOUND) {
+            int kept = 0;
+            for (int i = 0; i < n; ++i) kept += keep[i];
+            if (kept == 0) { flag = 1; for (int i = 0; i < n; ++i) keep[i] = 1; }
+        } else {
+            for (int i = 0; i < n; ++i) flag += (rule == FLAGG_W_CLIP) ? (info[i] > p0) : (float(info[i]) > float(p0));
+        }
+        if (rule != FLAGG_W_FLTRUST)
+            for (int i = 0; i < n; ++i) if (keep[i]) total += num_examples ? num_examples[i] : 1.0;   // integer counts in FP64: exact
+        for (int i = 0; i < n; ++i) {
+            if (keep[i]) {
+                rows[m] = i;
+                w1[m] = w1[i];      // m <= i: compaction in place never overwrites an unread entry
+                w2[m] = w2[i];
+                ++m;
+            }
+        }
+        for (int j = m; j < n; ++j) rows[j] = -1;
+        *divisor = float(total);
+        counts[0] = m;
+        counts[1] = flag;
+    }
+}
+
 }  // namespace flagg
 
 using namespace flagg;
 
 extern "C" {
+
+int flagg_round_weights(int rule, int n, const double* sumsq, const double* dot, const double* g0_sumsq, const float* linf,
+                        const double* num_examples, double p0, double p1, int32_t* rows, float* w1, float* w2, float* divisor,
+                        double* info, int32_t* counts, void* scratch_n_bytes, void* stream) {
+    FLAGG_REQUIRE(rule >= FLAGG_W_FLTRUST && rule <= FLAGG_W_NORMBOUND, "flagg_round_weights: bad rule %d", rule);
+    FLAGG_REQUIRE(n >= 1 && rows && w1 && w2 && divisor && info && counts && scratch_n_bytes, "flagg_round_weights: NULL argument");
+    FLAGG_REQUIRE(sumsq || linf, "flagg_round_weights: no statistics");
+    FLAGG_REQUIRE(rule != FLAGG_W_FLTRUST || (sumsq && dot && g0_sumsq), "flagg_round_weights: FLTrust needs sumsq, dot and g0_sumsq");
+    const int use_linf = (rule == FLAGG_W_CLIP && linf && !sumsq) ? 1 : 0;
+    FLAGG_REQUIRE(use_linf || sumsq, "flagg_round_weights: this rule needs sumsq");
+    round_weights_kernel<<<1, 256, 0, static_cast<cudaStream_t>(stream)>>>(rule, n, sumsq, dot, g0_sumsq, linf, num_examples, p0, p1,
+                                                                            use_linf, rows, w1, w2, divisor, info, counts,
+                                                                            static_cast<unsigned char*>(scratch_n_bytes));
+    FLAGG_CUDA(cudaGetLastError());
+    return FLAGG_OK;
+}
 
 int flagg_row_reduce(const flagg_view* cv, const float* g0, int centered, double* sumsq, double* dot, float* linf,
                      double* g0_sumsq, void* stream) {

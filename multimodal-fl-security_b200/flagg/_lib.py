@@ -45,6 +45,7 @@ def lib():
         "flagg_row_combine": (i32, [vp, i32, C.POINTER(C.c_int32), C.POINTER(f32), C.POINTER(f32), f32, vp, vp]),
         "flagg_row_combine_dev": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, vp, vp]),
         "flagg_weiszfeld_weights": (i32, [vp, i32, vp, vp, vp]),
+        "flagg_round_weights": (i32, [i32, i32, vp, vp, vp, vp, vp, C.c_double, C.c_double, vp, vp, vp, vp, vp, vp, vp, vp]),
         "flagg_gram": (i32, [vp, vp, i32, vp, vp]),
         "flagg_krum_scores": (i32, [vp, i32, i32, vp, vp, vp]),
         "flagg_krum_scores_from_distances": (i32, [vp, i32, i32, vp, vp]),
@@ -72,7 +73,7 @@ def lib():
 
 EXPORTS = ["flagg_version", "flagg_last_error", "flagg_device_info", "flagg_view_create", "flagg_view_destroy",
            "flagg_view_set_outputs", "flagg_row_combine_dev", "flagg_weiszfeld_weights", "flagg_krum_scores_from_distances", "flagg_segments_transform",
-           "flagg_sqdist", "flagg_krum_scores_from_sqdist", "flagg_view_cols", "flagg_view_rows", "flagg_colwise_select", "flagg_row_reduce", "flagg_row_combine",
+           "flagg_sqdist", "flagg_krum_scores_from_sqdist", "flagg_round_weights", "flagg_view_cols", "flagg_view_rows", "flagg_colwise_select", "flagg_row_reduce", "flagg_row_combine",
            "flagg_gram", "flagg_krum_scores", "flagg_colwise_select_host", "flagg_upload_rows", "flagg_host_release", "flagg_comm_unique_id",
            "flagg_comm_create", "flagg_comm_destroy", "flagg_comm_size", "flagg_comm_rank", "flagg_allreduce_f64",
            "flagg_allreduce_f32", "flagg_comm_scatter_columns"]

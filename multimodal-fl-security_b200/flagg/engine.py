@@ -364,6 +364,63 @@ def row_combine(u: Updates, rows, w1, w2, divisor: float, outputs=None) -> Optio
     return out
 
 
+W_FLTRUST, W_CLIP, W_DPSGD, W_NORMBOUND = 0, 1, 2, 3
+
+
+def weighted_round(u: Updates, rule: int, num_examples=None, g0_flat: Optional[torch.Tensor] = None, p0: float = 0.0,
+                   p1: float = 0.0, use_linf: bool = False, group=None, outputs=None):
+    """One clipping / trust round with the host out of the middle: K2 (row statistics) -> all-reduce when
+    sharded -> flagg_round_weights (the reference's per-client arithmetic on the device) -> K3 with
+    device-resident rows / weights / divisor.  Everything is enqueued back to back; the single read-back at the
+    end fetches what the defense reports (trust scores or norms, counts).
+    Returns (flat fp32 [d] on the device or None with ``outputs``, info float64 [n], kept, flag)."""
+    outs = u.check_outputs(outputs) if outputs is not None else None
+    u = u.resident()
+    n = u.n
+    L = lib()
+    with torch.cuda.device(u.device):
+        st = _stream()
+        buf = torch.zeros(2 * n + 1, dtype=torch.float64, device=u.device)
+        linf = torch.zeros(n, dtype=torch.float32, device=u.device)
+        g_ptr = None
+        if g0_flat is not None:
+            g0_flat = g0_flat.to(device=u.device, dtype=torch.float32).contiguous()
+            if g0_flat.numel() != u.d:
+                raise ValueError("g0 has the wrong number of elements")
+            g_ptr = g0_flat.data_ptr()
+        p = buf.data_ptr()
+        check(L.flagg_row_reduce(u.view(), g_ptr, 0, p, (p + 8 * n) if g_ptr else None, linf.data_ptr(),
+                                 (p + 16 * n) if g_ptr else None, st), "flagg_row_reduce")
+        if group is not None:
+            all_reduce(buf, group, "sum")
+            if use_linf:
+                all_reduce(linf, group, "max")
+        ne = None
+        if num_examples is not None:
+            ne = torch.tensor([float(int(x)) for x in num_examples], dtype=torch.float64).to(u.device, non_blocking=True)
+        rows = torch.empty(n, dtype=torch.int32, device=u.device)
+        w = torch.empty(2 * n + 1, dtype=torch.float32, device=u.device)          # w1, w2, divisor
+        info = torch.empty(n + 1, dtype=torch.float64, device=u.device)           # per-client value; the last slot holds the two counts
+        keep = torch.empty(n, dtype=torch.uint8, device=u.device)
+        wp = w.data_ptr()
+        check(L.flagg_round_weights(int(rule), n, None if use_linf else p, (p + 8 * n) if g_ptr else None,
+                                    (p + 16 * n) if g_ptr else None, linf.data_ptr() if use_linf else None,
+                                    ne.data_ptr() if ne is not None else None, float(p0), float(p1), rows.data_ptr(), wp, wp + 4 * n,
+                                    wp + 8 * n, info.data_ptr(), info.data_ptr() + 8 * n, keep.data_ptr(), st), "flagg_round_weights")
+        out = torch.empty(u.d, dtype=torch.float32, device=u.device) if outs is None else None
+        if outs is not None:
+            u._bind(outs)
+        try:
+            check(L.flagg_row_combine_dev(u.view(), n, rows.data_ptr(), wp, wp + 4 * n, wp + 8 * n,
+                                          out.data_ptr() if out is not None else None, None, None, st), "flagg_row_combine_dev")
+        finally:
+            if outs is not None:
+                u._bind(None)
+        h = info.cpu()                                                            # the round's one synchronisation
+        counts = h[n:].view(torch.int32)
+        return out, h[:n].numpy().copy(), int(counts[0]), int(counts[1])
+
+
 CENTER_ROWS = 31   # rows whose coordinate-wise median centres the Gram matrix
 
 

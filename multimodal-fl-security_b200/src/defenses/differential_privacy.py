@@ -61,8 +61,9 @@ class DPSGDDefense(BaseDefense):
     def aggregate(self, client_updates, num_examples):
         u = engine.Updates(client_updates)
         n = u.n
-        norms32 = _l2_norms32(engine.row_stats(u, group=self._group))
-        flat = self._weighted_mean(u, list(range(n)), num_examples, scale=self._scales(norms32))
+        # K2 -> (all-reduce) -> clip factors on the device (:90-92, fp32) -> K3, one read-back at the end
+        flat, _, _, _ = engine.weighted_round(u, engine.W_DPSGD, num_examples, p0=self.clip_norm, group=self._group,
+                                              outputs=self._outputs)
         aggregated = self._emit(u, flat, _out_dtypes(u))
         if flat is None:      # epilogue form: the noise of :112-117 lands in the model tensors too (same RNG calls)
             noise_std = self.clip_norm * self.noise_multiplier / n
@@ -129,10 +130,11 @@ class GradientClippingDefense(BaseDefense):
         self.clipped_count = 0
         self.original_norms = []
         u = engine.Updates(client_updates)
-        norms = self._norms(u)
-        self.original_norms = list(norms)
-        self.clipped_count = sum(1 for v in norms if v > self.clip_norm)
-        flat = self._weighted_mean(u, list(range(u.n)), num_examples, scale=[self._scale(v) for v in norms])
+        # K2 -> (all-reduce) -> clip factors on the device (:242-245: Python float clip / norm, then fp32) -> K3
+        flat, norms, _, clipped = engine.weighted_round(u, engine.W_CLIP, num_examples, p0=self.clip_norm,
+                                                        use_linf=self.clip_type == 'linf', group=self._group, outputs=self._outputs)
+        self.original_norms = norms.tolist()
+        self.clipped_count = clipped
         return self._emit(u, flat, _out_dtypes(u))
 
     def get_metrics(self) -> Dict[str, Any]:
@@ -150,16 +152,11 @@ class NormBoundingDefense(BaseDefense):
     def aggregate(self, client_updates, num_examples):
         self.rejected_clients = []
         u = engine.Updates(client_updates)
-        norms = [float(v) for v in _l2_norms32(engine.row_stats(u, group=self._group))]
-        keep = []
-        for i, nv in enumerate(norms):
-            if self.min_norm <= nv <= self.max_norm:          # :313
-                keep.append(i)
-            else:
-                self.rejected_clients.append(i)
-        if not keep:                                          # :319-322 all rejected -> use all
-            keep = list(range(u.n))
-        flat = self._weighted_mean(u, keep, num_examples)
+        # K2 -> (all-reduce) -> keep mask min <= norm <= max (:313; all rejected -> all used, :319-322) and the kept
+        # clients' example total on the device -> K3 over the kept rows
+        flat, norms, _, _ = engine.weighted_round(u, engine.W_NORMBOUND, num_examples, p0=self.max_norm, p1=self.min_norm,
+                                                  group=self._group, outputs=self._outputs)
+        self.rejected_clients = [i for i, nv in enumerate(norms.tolist()) if not (self.min_norm <= nv <= self.max_norm)]
         return self._emit(u, flat, _out_dtypes(u))
 
     def detect_malicious(self, client_updates, num_examples) -> List[int]:

@@ -107,22 +107,17 @@ class FLTrustDefense(BaseDefense):
             if hi - lo != u.d:
                 raise ValueError(f"sharded FLTrust: this rank's updates hold {u.d} columns, its shard of g0 is [{lo}, {hi})")
             g0 = g0[lo:hi]
-        st = engine.row_stats(u, g0, group=self._group)
-        self.trust_scores, scale = self._trust_from_stats(st)
-        total_trust = sum(self.trust_scores)
-        if total_trust < 1e-10:                                                 # :258-260
+        # K2 -> all-reduce -> trust scores / renormalisation on the device -> K3: no host round trip in the middle
+        # (the fp32 arithmetic of fltrust.py:174-186, 208-214 and Python's double-precision sum(trust), :256)
+        flat, info, _, no_trust = engine.weighted_round(u, engine.W_FLTRUST, None, g0, group=self._group, outputs=self._outputs)
+        self.trust_scores = info.tolist()
+        if no_trust:                                                            # sum(trust) < 1e-10 -> g0 (:258-260)
             if self._outputs is not None:
                 u.scatter(g0.to(u.device), u.check_outputs(self._outputs))
                 return list(self._outputs)
             if sharded:
                 return u.split(g0.to(u.device), to_host=u.on_host)
             return server_gradient
-        # Zero-trust rows contribute exactly +-0 to the running sum (which starts at +0 and
-        # can never be -0), so they are skipped unless the row holds Inf/NaN (0*Inf = NaN).
-        rows = [i for i in range(u.n) if self.trust_scores[i] != 0.0 or not np.isfinite(st['sumsq'][i])]
-        flat = engine.row_combine(u, rows, [scale[i] for i in rows],
-                                  [np.float32(self.trust_scores[i]) for i in rows], np.float32(total_trust),
-                                  outputs=self._outputs)
         dt = [d if d.is_floating_point else torch.float32 for d in u.in_dtypes]
         out = self._emit(u, flat, dt)
         u.close()
