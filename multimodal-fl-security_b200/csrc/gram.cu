@@ -201,13 +201,13 @@ int flagg_gram(const flagg_view* cv, const float* center, int accumulate, double
     v->last_stream = stream;
     const int n = v->dev.n;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    {   // Kernel choice (FLAGG_GRAM_IMPL=small|ffma|tc|ss|ts|ts1|ts2 overrides, see gram_tc_launch):
+    {   // Kernel choice (FLAGG_GRAM_IMPL=small|ffma|tc|ss|ts1|ts2 overrides, see gram_tc_launch):
         //   n <= 32            register-tile kernel (gram_small.cu), any alignment
         //   n >= 33, aligned   tensor cores (gram_tc.cu: single CTAs up to n = 128, CTA pairs above)
         //   otherwise          64x64 FFMA tiles (below)
         const char* impl = getenv("FLAGG_GRAM_IMPL");
         auto is = [&](const char* name) { return impl && !strcmp(impl, name); };
-        const bool force_tc = is("tc") || is("ss") || is("ts") || is("ts1") || is("ts2"), force_ffma = is("ffma"), force_small = is("small");
+        const bool force_tc = is("tc") || is("ss") || is("ts1") || is("ts2"), force_ffma = is("ffma"), force_small = is("small");
         if (force_tc && v->align_bytes < 16) {
             set_error("flagg_gram: FLAGG_GRAM_IMPL=tc needs 16-byte aligned tensors");
             return FLAGG_EUNSUPPORTED;

@@ -484,15 +484,14 @@ int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G
     FLAGG_REQUIRE(sms > 0, "cannot query the SM count of the current device");
     const char* impl = getenv("FLAGG_GRAM_IMPL");
     auto is = [&](const char* name) { return impl && !strcmp(impl, name); };
-    const bool want_ss = is("ss"), want_ts = is("ts"), want_ts2 = is("ts2"), want_ts1 = is("ts1");
-    const bool forced = want_ss || want_ts || want_ts2 || want_ts1;
+    const bool want_ss = is("ss"), want_ts2 = is("ts2"), want_ts1 = is("ts1");
+    const bool forced = want_ss || want_ts2 || want_ts1;
     // measured: one (diagonal) pair tile beats three 128x128 tiles from n = 129 (tools/k4_small_n.py)
     const bool pair = want_ts2 || (!forced && n > TILE);
     const bool single = want_ts1 || (!forced && n <= TILE);
     static bool attr_set = false;
     if (!attr_set) {
         FLAGG_CUDA(cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-        FLAGG_CUDA(cudaFuncSetAttribute(gram_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_BYTES));
         FLAGG_CUDA(cudaFuncSetAttribute(gram_ts2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
         FLAGG_CUDA(cudaFuncSetAttribute(gram_ts1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, T2_SMEM_BYTES));
         attr_set = true;
@@ -550,8 +549,7 @@ int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G
     if (rc != FLAGG_OK) return rc;
     double* part = static_cast<double*>(v->d_scratch);
     dim3 grid(tiles, unsigned(splits));
-    if (want_ts) gram_ts_kernel<<<grid, THREADS, TS_SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
-    else gram_tc_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
+    gram_tc_kernel<<<grid, THREADS, SMEM_BYTES, st>>>(v->dev, center, nb, units, upb, part);
     FLAGG_CUDA(cudaGetLastError());
     gram_tc_reduce_kernel<<<dim3(tiles, 16), 256, 0, st>>>(part, tiles, int(splits), nb, n, accumulate, G);
     FLAGG_CUDA(cudaGetLastError());

@@ -1,6 +1,8 @@
-// K4, "TS" variant: the A operand of every tcgen05.mma comes from TENSOR MEMORY, B from
-// shared memory.  Included by gram_tc.cu inside namespace flagg::tc (shares its PTX wrappers,
-// KbIter and the reduce kernel).  Replaces krum.py:92-97 like the SS kernel does.
+// K4, "TS" form: the A operand of every tcgen05.mma comes from TENSOR MEMORY, B from shared memory.
+// This header holds what the TS kernels share -- the TMEM store / MMA wrappers, the producers' load and hi/lo
+// split, the K permutation -- and is included by gram_tc.cu inside namespace flagg::tc before gram_ts2.cuh.
+// (The first TS kernel, 128 x 128 tiles per CTA, 32.9 ms on the C4 shard, was superseded by the CTA-pair and
+// single-CTA kernels of gram_ts2.cuh and removed in round 2; its measurements stay in DESIGN.md.)
 //
 // Why: with both operands in shared memory a 128x128x8 tf32 MMA reads 8 KB of smem in its 64
 // cycles -- the whole 128 B/clk the SM has -- and the producers' hi/lo stores (85 B/clk at
@@ -129,209 +131,5 @@ __device__ __forceinline__ void ts_split(const float (&x)[8], const float (&c)[8
         const float t = __fsub_rn(x[j], c[j]);
         hi[j] = __float_as_uint(t) & mask;
         lo[j] = __float_as_uint(__fsub_rn(t, __uint_as_float(__float_as_uint(t) & 0xffffe000u))) & mask;
-    }
-}
-
-__global__ void __launch_bounds__(THREADS, 1)
-gram_ts_kernel(ViewDev v, const float* __restrict__ center, int nb, int64_t total_units, int64_t units_per_split,
-               double* __restrict__ part) {
-    extern __shared__ unsigned char smem_raw[];
-    const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    unsigned char* smem = smem_raw + (sbase - smem_u32(smem_raw));
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TS_SLOTS * TS_SLOT_BYTES);
-    // bars[0..NSTG) full, [NSTG..2NSTG) empty, then 2 tmem_full, 2 tmem_empty
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TS_NSTG + 4);
-    int* nkb_slot = reinterpret_cast<int*>(bars + 2 * TS_NSTG + 6);
-    const uint32_t bar0 = sbase + TS_SLOTS * TS_SLOT_BYTES;
-    auto FULL = [&](int s) { return bar0 + 8u * s; };
-    auto EMPTY = [&](int s) { return bar0 + 8u * (TS_NSTG + s); };
-    auto TFULL = [&](int b) { return bar0 + 8u * (2 * TS_NSTG + b); };
-    auto TEMPTY = [&](int b) { return bar0 + 8u * (2 * TS_NSTG + 2 + b); };
-
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    int t = blockIdx.x, bi = 0;
-    while (t >= nb - bi) { t -= nb - bi; ++bi; }
-    const int bj = bi + t;
-    const bool diag = (bi == bj);
-    const int64_t u0 = int64_t(blockIdx.y) * units_per_split;
-    const int64_t u1 = min(total_units, u0 + units_per_split);
-
-    if (tid == 0) {
-        for (int s = 0; s < TS_NSTG; ++s) { mbar_init(FULL(s), PROD_WARPS); mbar_init(EMPTY(s), 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(TFULL(b), 1); mbar_init(TEMPTY(b), EPI_WARPS); }
-        fence_barrier_init();
-        *nkb_slot = int(count_kblocks(v, u0, u1));
-    }
-    if (warp == MMA_WARP) tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
-    const int nkb = *nkb_slot;
-    const int ndrain = (nkb + KC_BLOCKS - 1) / KC_BLOCKS;
-
-    if (warp >= EPI_WARPS && warp < MMA_WARP) {
-        // ================================ producers ================================
-        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(TS_PROD_REGS));
-        const int qd = warp & 3, half = (warp - EPI_WARPS) >> 2;
-        const int lane0 = 32 * qd + 16 * half;          // first TMEM lane / tile row of this warp
-        const int rloc = lane0 + (lane >> 2), q = lane & 3;
-        // byte offset of K position 2q of tile row rloc inside a swizzled operand tile; K position
-        // 8g + 2q is the same offset ^ (g << 5) (16-byte chunk index 2g + q/2, XOR-swizzled by row & 7)
-        const uint32_t off0 = uint32_t(rloc >> 3) * 1024u + uint32_t(rloc & 7) * 128u +
-                              (uint32_t((q >> 1) ^ (rloc & 7)) << 4) + uint32_t(q & 1) * 8u;
-        bool okA[2], okB[2];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            okA[h] = (bi * TILE + rloc + 8 * h) < v.n;
-            okB[h] = (bj * TILE + rloc + 8 * h) < v.n;
-        }
-        // rows >= n of B stay zero for the whole kernel (their stores are predicated off)
-        for (int s = 0; s < TS_SLOTS; ++s)
-            for (int o = 0; o < 2; ++o)
-#pragma unroll
-                for (int h = 0; h < 2; ++h)
-#pragma unroll
-                    for (int g = 0; g < 4; ++g)
-                        *reinterpret_cast<uint2*>(smem + s * TS_SLOT_BYTES + o * OPER_BYTES + ((off0 + h * 1024u) ^ (uint32_t(g) << 5))) =
-                            make_uint2(0u, 0u);
-        TsRows rows;
-        int cur_p = -1;
-        auto refresh_rows = [&](int p) {
-            uintptr_t bits = 0;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int ra = min(bi * TILE + rloc + 8 * h, v.n - 1), rb = min(bj * TILE + rloc + 8 * h, v.n - 1);
-                rows.a[h] = v.seg_ptrs[size_t(ra) * v.P + p];
-                rows.b[h] = v.seg_ptrs[size_t(rb) * v.P + p];
-                bits |= reinterpret_cast<uintptr_t>(rows.a[h]) | reinterpret_cast<uintptr_t>(rows.b[h]);
-            }
-            rows.cbase = center ? center + v.seg_start[p] : nullptr;
-            rows.v8 = (bits & 31) == 0;
-            cur_p = p;
-        };
-        KbIter it;
-        it.init(v, u0, u1);
-        TsRegs r0, r1;
-        auto fetch = [&](TsRegs& r) {
-            if (it.valid()) {
-                if (it.p != cur_p) refresh_rows(it.p);
-                ts_load(it, rows, diag, q, r);
-                it.next(v);
-            }
-        };
-        fetch(r0);
-        fetch(r1);
-        int stage = 0;
-        uint32_t phase = 1;
-        const uint32_t a_lane = tmem_base + (uint32_t(lane0) << 16) + TS_TMEM_A0;
-        auto emit = [&](const TsRegs& r) {
-            uint32_t ahi[2][8], alo[2][8], bhi[2][8], blo[2][8];
-#pragma unroll
-            for (int h = 0; h < 2; ++h) ts_split(r.a[h], r.c, okA[h] ? 0xffffe000u : 0u, ahi[h], alo[h]);
-            if (!diag) {
-#pragma unroll
-                for (int h = 0; h < 2; ++h) ts_split(r.b[h], r.c, 0xffffe000u, bhi[h], blo[h]);
-            } else {   // B rows are the A rows (okB == okA); stores of padding rows are predicated off below
-#pragma unroll
-                for (int h = 0; h < 2; ++h)
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) { bhi[h][j] = ahi[h][j]; blo[h][j] = alo[h][j]; }
-            }
-#pragma unroll
-            for (int sub = 0; sub < TS_SUBS; ++sub) {
-                mbar_wait(EMPTY(stage), phase);
-                tc_fence_after();
-                // A -> TMEM: register 4*gl + 2*h + e of the fragment = row h, value j = 2*(g0+gl) + e
-                constexpr int NG = TS_SK / 8;
-                static_assert(NG == 2, "fragment wrappers below are .x2");
-                uint32_t fh[8], fl[8];
-#pragma unroll
-                for (int gl = 0; gl < NG; ++gl)
-#pragma unroll
-                    for (int h = 0; h < 2; ++h)
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            fh[4 * gl + 2 * h + e] = ahi[h][2 * (sub * NG + gl) + e];
-                            fl[4 * gl + 2 * h + e] = alo[h][2 * (sub * NG + gl) + e];
-                        }
-                tmem_st_16x256b_x2(a_lane + uint32_t(stage * 2 * TS_SK), fh);
-                tmem_st_16x256b_x2(a_lane + uint32_t(stage * 2 * TS_SK + TS_SK), fl);
-                // B -> smem (same K permutation): value pair (2g, 2g+1) -> K positions 8g + 2q + {0,1}
-                const uint32_t sb = sbase + uint32_t(stage / TS_SUBS) * TS_SLOT_BYTES;
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const bool ok = okB[h];
-#pragma unroll
-                    for (int gl = 0; gl < NG; ++gl) {
-                        const int g = sub * NG + gl;
-                        const uint32_t addr = sb + ((off0 + h * 1024u) ^ (uint32_t(g) << 5));
-                        if (ok) {
-                            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(bhi[h][2 * g]), "r"(bhi[h][2 * g + 1]) : "memory");
-                            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr + OPER_BYTES), "r"(blo[h][2 * g]), "r"(blo[h][2 * g + 1]) : "memory");
-                        }
-                    }
-                }
-                tmem_wait_st();
-                tc_fence_before();
-                fence_proxy_async();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(FULL(stage));
-                if (++stage == TS_NSTG) { stage = 0; phase ^= 1; }
-            }
-        };
-        for (int kb = 0; kb < nkb; kb += 2) {
-            emit(r0);
-            fetch(r0);
-            if (kb + 1 < nkb) {
-                emit(r1);
-                fetch(r1);
-            }
-        }
-    } else if (warp == MMA_WARP) {
-        // ================================ MMA issuer ================================
-        int s = 0, inb = 0, buf = 0;
-        uint32_t full_phase = 0, tempty_phase = 3u;
-        for (int kb = 0; kb < nkb; ++kb) {
-            if (inb == 0) {
-                mbar_wait(TEMPTY(buf), (tempty_phase >> buf) & 1u);
-                tempty_phase ^= 1u << buf;
-                tc_fence_after();
-            }
-            const bool last_in_drain = (inb == KC_BLOCKS - 1) || (kb == nkb - 1);
-            const uint32_t d = tmem_base + uint32_t(buf * TILE);
-#pragma unroll
-            for (int sub = 0; sub < TS_SUBS; ++sub) {
-                mbar_wait(FULL(s), full_phase);
-                tc_fence_after();
-                if (lane == 0) {
-                    const uint32_t b_hi = sbase + uint32_t(s / TS_SUBS) * TS_SLOT_BYTES, b_lo = b_hi + OPER_BYTES;
-                    const uint32_t a_hi = tmem_base + TS_TMEM_A0 + uint32_t(s * 2 * TS_SK), a_lo = a_hi + TS_SK;
-#pragma unroll
-                    for (int k = 0; k < TS_SK / UMMA_K; ++k) {
-                        const uint32_t ko = uint32_t((s % TS_SUBS) * TS_SK + k * UMMA_K) * 4u;   // K byte offset inside the 128-byte row
-                        const uint32_t ka = uint32_t(k * UMMA_K);
-                        umma_tf32_ts(d, a_hi + ka, make_desc(b_hi + ko), (inb > 0 || sub > 0 || k > 0) ? 1u : 0u);
-                        umma_tf32_ts(d, a_hi + ka, make_desc(b_lo + ko), 1u);
-                        umma_tf32_ts(d, a_lo + ka, make_desc(b_hi + ko), 1u);
-                    }
-                    umma_commit(EMPTY(s));
-                    if (last_in_drain && sub == TS_SUBS - 1) umma_commit(TFULL(buf));
-                }
-                __syncwarp();
-                if (++s == TS_NSTG) { s = 0; full_phase ^= 1; }
-            }
-            if (last_in_drain) { inb = 0; buf ^= 1; } else { ++inb; }
-        }
-    } else {
-        // ================================ epilogue ================================
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(TS_EPI_REGS));
-        epilogue_role(tmem_base, part, ndrain, warp, lane, TFULL(0), TEMPTY(0));
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == MMA_WARP) {
-        tc_fence_after();
-        tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }

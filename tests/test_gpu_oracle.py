@@ -308,13 +308,13 @@ def test_gram_distances_scores_vs_fp64(n, d, f):
     u.close()
 
 
-@pytest.mark.parametrize("impl", ["tc", "ss", "ts", "ts1", "ts2", "ffma"])
+@pytest.mark.parametrize("impl", ["tc", "ss", "ts1", "ts2", "ffma"])
 @pytest.mark.parametrize("n,seg,f", [(64, [4096], 10), (128, [32], 20), (65, [3000], 10), (130, [2048, 1], 20),
                                      (200, [780, 64, 5000], 50), (257, [33, 95, 4100], 60), (600, [5000, 77, 1300], 100),
                                      (1000, [7000, 36, 3000], 100)])
 def test_gram_paths_vs_fp64(n, seg, f, impl, monkeypatch):
     """K4 on the tensor cores (tcgen05 3xTF32: "tc" = the dispatcher's choice, "ss" = 128x128 tiles
-    with both operands in shared memory, "ts" = A operand from tensor memory, "ts2" = 256x256
+    with both operands in shared memory, "ts2" = 256x256
     CTA-pair tiles, gram_tc.cu / gram_ts.cuh / gram_ts2.cuh) and on the CUDA cores (gram.cu), forced
     through FLAGG_GRAM_IMPL, against FP64: distances within 1e-5 relative (north_star), exact
     symmetry, zero distance between exact duplicates, identical Krum selection.  Ragged segment
@@ -518,7 +518,7 @@ def test_gram_tc_is_default_for_large_n_and_falls_back_when_unaligned(monkeypatc
     u_al.close(); u_unal.close()
 
 
-@pytest.mark.parametrize("impl,n", [("ss", 96), ("ts", 96), ("ts1", 96), ("ts1", 300), ("ts2", 96), ("ts2", 300)])
+@pytest.mark.parametrize("impl,n", [("ss", 96), ("ts1", 96), ("ts1", 300), ("ts2", 96), ("ts2", 300)])
 def test_gram_tensor_core_paths_on_16_byte_aligned_views(impl, n, monkeypatch):
     """Rows that are views of one matrix with a 16-byte (not 32-byte) multiple pitch: the
     tensor-core producers must take their 128-bit load path; centred Gram against FP64."""

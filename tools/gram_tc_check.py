@@ -66,11 +66,11 @@ def tf32_peak():
 if __name__ == "__main__":
     bad = 0
     if "--only-time" in sys.argv:
-        timing(int(os.environ.get("K4_N", 1000)), int(os.environ.get("K4_D", 3_125_000)), sys.argv[-1] if sys.argv[-1] in ("tc", "ss", "ts", "ts1", "ts2", "small", "ffma") else "tc", reps=2)
+        timing(int(os.environ.get("K4_N", 1000)), int(os.environ.get("K4_D", 3_125_000)), sys.argv[-1] if sys.argv[-1] in ("tc", "ss", "ts1", "ts2", "small", "ffma") else "tc", reps=2)
         sys.exit(0)
     if "--peak" in sys.argv:
         tf32_peak()
-    IMPLS = [a for a in sys.argv[1:] if a in ("tc", "ss", "ts", "ts1", "ts2", "ffma")] or ["tc", "ss", "ts2", "ffma"]
+    IMPLS = [a for a in sys.argv[1:] if a in ("tc", "ss", "ts1", "ts2", "ffma")] or ["tc", "ss", "ts2", "ffma"]
     for n, segs in [(64, [4096]), (257, [4096 + 32]), (600, [5000, 77, 130000]), (128, [32]), (128, [256 * 40]), (65, [3000]), (130, [2049 - 1, 1]), (200, [777 + 3, 64, 5000]),
                     (300, [100000]), (1000, [70000, 36, 30000])]:
         for impl in IMPLS:
