@@ -111,31 +111,45 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.samples, self.proc, self.index = [], None, index
+        self.samples, self.proc, self.index, self.t0, self.t1 = [], None, index, None, None
 
     def start(self):
+        """Started early (nvidia-smi needs ~0.2 s before its first line); mark() brackets the timed region."""
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "20", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
 
     def _read(self):
         for line in self.proc.stdout:
-            self.samples.append([x.strip() for x in line.split(",")])
+            self.samples.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
+
+    def mark(self):
+        if self.t0 is None:
+            self.t0 = time.perf_counter()
+        else:
+            self.t1 = time.perf_counter()
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.05)
         self.proc.terminate()
-        rows = [r for r in self.samples if len(r) == 6 and r[0].isdigit()]
+        ok = [(t, r) for t, r in self.samples if len(r) == 6 and r[0].isdigit()]
+        t0, t1 = self.t0 or 0.0, self.t1 or float("inf")
+        rows = [r for t, r in ok if t0 <= t <= t1 + 0.03]          # samples taken while the warm-up + timed steps ran
+        window = "warm-up + timed steps"
+        if not rows and ok:                                         # a 40 ms region can fall between two samples: nearest ones
+            rows = [r for _, r in sorted(ok, key=lambda tr: abs(tr[0] - t1))[:3]]
+            window = "nearest to the timed steps"
         if not rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({nm for r in rows for nm, v in zip(names, r[2:]) if v.lower().startswith("active")})
         return {"sm_mhz": float(np.median([int(r[0]) for r in rows])), "sm_max_mhz": int(rows[0][1]),
-                "reasons": reasons, "samples": len(rows)}
+                "reasons": reasons, "samples": len(rows), "window": window}
 
 
 def synth_rows(n, d, n_byz, seed, device="cuda", theta_sigma=0.05, spread=0.0):
@@ -649,6 +663,9 @@ def run_flagg(args, rank, world, local_rank):
     comm = engine.Comm.from_torch() if dist_on else None
     parity = sharded_parity_check(comm, rank, world) if dist_on else None
 
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
     n, d = N_CLIENTS, D_PARAMS
     X = synth_rows(n, d, 10, 1234 + rank)
     u = engine.Updates([[X[i]] for i in range(n)])
@@ -659,10 +676,11 @@ def run_flagg(args, rank, world, local_rank):
     def step():
         check(lib().flagg_colwise_select(view, MEDIAN, 0, out.data_ptr(), stream), "flagg_colwise_select")
 
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    step()
+    torch.cuda.synchronize()
+    sampler.mark()
     t = time_steps(step, args.steps, args.warmup, dist_on)
+    sampler.mark()
     clocks = sampler.stop() if rank == 0 else None
     ms = t / args.steps * 1e3
     value = world * 4.0 * n * d * args.steps / t / 1e9
