@@ -15,6 +15,8 @@ Beside the headline the line carries
   roofline       the dominant kernel against the measured HBM rate
   plugin_device  the same median through MedianDefense.aggregate on SEPARATELY ALLOCATED device
                  rows (the run_experiments.py:238 layout: pointer-table view, no dense matrix)
+  plugin_device_resnet50  the simulator's real call: 100 clients x the 161 parameter tensors of the reference's
+                 ResNet-50, every tensor its own allocation (16,100 tensor handles per aggregate() call)
   e2e            the same median through the plugin call with pinned HOST tensors (Flower path)
   e2e_pageable   Krum / FLTrust through the plugin call on pageable, separately allocated host
                  tensors (the torch.tensor(ndarray) layout of robust_server.py:99-104)
@@ -304,6 +306,38 @@ def separate_rows(X):
     """One allocation per client (run_experiments.py:238: ``[p.data.clone() ...]``): rows at
     unrelated addresses, so flagg_view_create cannot describe them as one dense matrix."""
     return [[torch.empty(X.shape[1], dtype=torch.float32, device=X.device).copy_(X[i])] for i in range(X.shape[0])]
+
+
+def resnet50_param_sizes(num_classes=200):
+    """Parameter tensor sizes of the reference's CUB200CNN (torchvision ResNet-50 + a 200-way head,
+    src/models/cub200_cnn.py:26-29) in model.parameters() order: 161 tensors, 23,917,832 parameters."""
+    sizes = [64 * 3 * 7 * 7, 64, 64]
+    inplanes = 64
+    for planes, blocks in ((64, 3), (128, 4), (256, 6), (512, 3)):
+        for b in range(blocks):
+            sizes += [planes * inplanes, planes, planes, planes * planes * 9, planes, planes, planes * 4 * planes, planes * 4, planes * 4]
+            if b == 0:
+                sizes += [planes * 4 * inplanes, planes * 4, planes * 4]
+            inplanes = planes * 4
+    return sizes + [num_classes * 2048, num_classes]
+
+
+def plugin_device_resnet50(steps):
+    """The simulator's actual call (run_experiments.py:236-244): 100 clients, each update a list of the model's 161
+    parameter tensors, every tensor its own allocation (``p.data.clone()``) -- 16,100 tensor handles per call."""
+    from src.defenses import MedianDefense
+    sizes = resnet50_param_sizes()
+    n, d = N_CLIENTS, sum(sizes)
+    g = torch.Generator(device="cuda").manual_seed(7)
+    theta = [torch.randn(s, device="cuda", generator=g) * 0.05 for s in sizes]
+    ups = [[t + torch.randn(t.numel(), device="cuda", generator=g) * (1e-2 if i < 10 else 1e-3) for t in theta] for i in range(n)]
+    defense = MedianDefense({})
+    t = time_steps(lambda: defense.aggregate(ups, [1] * n), steps, 3, False) / steps
+    hbm, _ = peaks()
+    del ups
+    return {"ms": t * 1e3, "GBps": 4.0 * n * d / t / 1e9, "frac": 4.0 * d * (n + 1) / t / 1e9 / hbm, "steps": steps,
+            "n_clients": n, "n_params": d, "tensors_per_client": len(sizes),
+            "api": "src.defenses.MedianDefense.aggregate(100 clients x 161 separately allocated ResNet-50 parameter tensors)"}
 
 
 def plugin_device_median(X, steps, dist_on, world):
@@ -695,9 +729,10 @@ def run_flagg(args, rank, world, local_rank):
     del X, u, out
     torch.cuda.empty_cache()
     with_cpu = world == 1 and not args.no_cpu
-    extras, strong, pageable = {}, None, None
+    extras, strong, pageable, plugin_r50 = {}, None, None, None
     if not args.no_extras:
         if rank == 0:
+            plugin_r50 = plugin_device_resnet50(10)
             pageable = e2e_pageable() if not args.no_e2e else None
             extras = c2_defenses(False, with_cpu)
         if dist_on:
@@ -716,7 +751,7 @@ def run_flagg(args, rank, world, local_rank):
                          "traffic": ncu_traffic("colselect_bulk_kernel<100,median>"), "peak_source": which,
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel": "colselect_bulk_kernel<100, MEDIAN_EXACT> (2-D TMA feed; the input is one dense matrix)"},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "plugin_device": plugin, "e2e_pageable": pageable, "strong": strong, "defenses": extras,
+            "plugin_device": plugin, "plugin_device_resnet50": plugin_r50, "e2e_pageable": pageable, "strong": strong, "defenses": extras,
         }
         if dist_on:
             line["sharded_parity"] = parity

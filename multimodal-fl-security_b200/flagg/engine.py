@@ -130,6 +130,20 @@ def all_reduce(t: torch.Tensor, group, op: str = "sum") -> torch.Tensor:
     return t
 
 
+_HOSTWALK = False     # flagg/_hostwalk*.so (csrc/hostwalk.cpp): resolved on first use; None when it was not built
+
+
+def _hostwalk():
+    global _HOSTWALK
+    if _HOSTWALK is False:
+        try:
+            from . import _hostwalk as mod
+            _HOSTWALK = mod
+        except ImportError:
+            _HOSTWALK = None
+    return _HOSTWALK
+
+
 class Updates:
     """n client updates of P tensors each, as the defenses receive them
     (base_defense.py:31-35).  Device tensors are used in place; host tensors stay on the
@@ -143,6 +157,26 @@ class Updates:
         if self.P == 0:
             raise ValueError("client updates hold no tensors")
         first = client_updates[0]
+        self._view = None
+        self._dense = None
+        self._ptrs = None
+        hw = _hostwalk()
+        if hw is not None and isinstance(client_updates, (list, tuple)):
+            # native walk: validates the n x P handles (fp32, contiguous, grad-free, one device, consistent sizes) and
+            # fills the pointer table in one pass, ~20 ns per tensor instead of ~0.8 us; anything else -- a conversion
+            # to make, an error to report -- takes the general loop below, which words the error
+            table = (C.c_void_p * (self.n * self.P))()
+            status, n, P, on_host, _dev = hw.walk(client_updates, C.addressof(table))
+            if status == 0:
+                self.shapes = [tuple(t.shape) for t in first]
+                self.numel = [int(t.numel()) for t in first]
+                self.in_dtypes = [torch.float32] * self.P
+                self.d = int(sum(self.numel))
+                self.on_host = bool(on_host)
+                self.device = first[0].device
+                self.rows = client_updates          # the caller's own lists: they keep every tensor alive
+                self._ptrs = table
+                return
         self.shapes = [tuple(t.shape) for t in first]
         self.numel = [int(t.numel()) for t in first]
         self.in_dtypes = [t.dtype for t in first]
@@ -169,12 +203,12 @@ class Updates:
                 push(t)
             rows.append(row)
         self.rows = rows          # keeps every tensor alive while a view points at it
-        self._view = None
-        self._dense = None
 
     # -- views ---------------------------------------------------------------------
     def _ptr_tables(self):
         seg = (C.c_int64 * self.P)(*self.numel)
+        if self._ptrs is not None:
+            return seg, self._ptrs
         ptrs = (C.c_void_p * (self.n * self.P))()
         k = 0
         for row in self.rows:
