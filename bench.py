@@ -749,7 +749,7 @@ def run_flagg(args, rank, world, local_rank):
             "config": dict(CONFIG), "clients_x_params_per_s": world * n * d * args.steps / t,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                          "traffic": ncu_traffic("colselect_bulk_kernel<100,median>"), "peak_source": which,
-                         "algorithmic_bytes_per_launch": alg_bytes, "kernel": "colselect_bulk_kernel<100, MEDIAN_EXACT> (2-D TMA feed; the input is one dense matrix)"},
+                         "algorithmic_bytes_per_launch": alg_bytes, "kernel": "colselect_bulk_kernel<100, MEDIAN_EXACT, 256> (2-D TMA boxes of 256 columns x 100 rows; the input is one dense matrix)"},
             "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "plugin_device": plugin, "plugin_device_resnet50": plugin_r50, "e2e_pageable": pageable, "strong": strong, "defenses": extras,
         }

@@ -164,7 +164,7 @@ extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float*
         }
         // dense matrix -> one 2-D box per tile; separately allocated 512-byte-congruent rows -> gather4 (four clients per request)
         const int flag = (want_bulk && exact && v->align_bytes >= 16 && (v->dense || v->gather)) ? CS_BULK : 0;
-        const bool wide = flag && !v->dense && v->dev.gather_cols == 256 && e->n <= CSB_WIDE_MAX_N;
+        const bool wide = flag && e->n <= CSB_WIDE_MAX_N && (v->dense ? v->dev.dense_cols == 256 : v->dev.gather_cols == 256);
         return e->fn(v->dev, variant | flag | (wide ? CS_WIDE : 0), k, out, wide ? v->total_units[GRAN_256] : units, sms, st);
     }
     {   // shared-memory tile select (colselect_tile.cu): one HBM read instead of 8-17.  Measured against the radix

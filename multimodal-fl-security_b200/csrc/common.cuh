@@ -40,6 +40,7 @@ struct ViewDev {
     // CUtensorMap[P] (64 B each, device memory) when every tensor is one dense [n x len] matrix
     // with a 16-byte-multiple row pitch -- box {128 columns, n rows}; nullptr otherwise.
     const void* tmaps;
+    int dense_cols;                // columns per tmaps box: 256 (n <= 110) or 128
     // Separately allocated rows (the reference's list-of-lists, run_experiments.py:238): ONE CUtensorMap
     // over the address range [min pointer, max end) seen as a 2-D fp32 matrix of 128-column (512-byte)
     // rows, and seg_rows[p][i] = (seg_ptrs[i*P+p] - min pointer) / 512 ([P][n rounded up to 4], padded with client n-1).  A 128-column unit of any

@@ -141,7 +141,16 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
             if (!ok) break;
             const cuuint64_t gdim[2] = {cuuint64_t(v->seg_numel[p]), cuuint64_t(n)};
             const cuuint64_t gstride[1] = {cuuint64_t(pitch)};
-            const cuuint32_t box[2] = {128u, cuuint32_t(n)};
+            // 256-column boxes (two 256-thread CTAs per SM: eight warps in one barrier domain share their instruction
+            // fetches, no_instruction stalls 0.72 -> 0.17 per issue) where the networks are issue-bound, 80 <= n <= 110:
+            // C3 2.03 -> 1.995 ms; 128-column boxes (3-4 CTAs of 128) elsewhere -- the HBM-bound sizes measured 2-8 %
+            // slower with the wide form (profiles/r02_k1_layouts.txt).  FLAGG_K1_DENSE_COLS=128|256 forces one (tests).
+            const char* dc = getenv("FLAGG_K1_DENSE_COLS");
+            cuuint32_t bcols = (n >= 80 && n <= 110) ? 256u : 128u;
+            if (dc && atoi(dc) == 128) bcols = 128u;
+            if (dc && atoi(dc) == 256 && n <= 110) bcols = 256u;
+            v->dev.dense_cols = int(bcols);
+            const cuuint32_t box[2] = {bcols, cuuint32_t(n)};
             const cuuint32_t estride[2] = {1u, 1u};
             const CUresult r = encode(&tmaps[p], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<char*>(r0), gdim, gstride, box,
                                       estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,

@@ -66,7 +66,7 @@ def dense_lists(X, seg, pitch_pad=4):
     return big, [[big[i, offs[p]:offs[p + 1]] for p in range(len(seg))] for i in range(n)]
 
 
-@pytest.mark.parametrize("impl", ["default", "ldg", "bulk"])
+@pytest.mark.parametrize("impl", ["default", "ldg", "bulk", "bulk256"])
 @pytest.mark.parametrize("n", [2, 3, 5, 10, 16, 20, 31, 32, 36, 48, 64, 72, 96, 100, 128])
 def test_median_and_trimmed_dense_tma_path(n, impl, monkeypatch):
     """K1 fed by TMA (2-D tensor-map boxes on a dense matrix; per-row 1-D bulk copies when forced
@@ -74,8 +74,14 @@ def test_median_and_trimmed_dense_tma_path(n, impl, monkeypatch):
     +-0 / NaN / Inf columns, ragged tails (tensor lengths not multiples of 128 columns, zero-filled
     by the TMA unit) and several tensors per client."""
     from flagg import MEDIAN, TRIMMED_MEAN, engine
+    monkeypatch.delenv("FLAGG_K1_DENSE_COLS", raising=False)
     if impl == "default":
         monkeypatch.delenv("FLAGG_K1_IMPL", raising=False)
+    elif impl == "bulk256":                                            # 256-column boxes at every n they serve (default: 80..110)
+        if n > 110:
+            pytest.skip("256-column tiles serve n <= 110")
+        monkeypatch.setenv("FLAGG_K1_IMPL", "bulk")
+        monkeypatch.setenv("FLAGG_K1_DENSE_COLS", "256")
     else:
         monkeypatch.setenv("FLAGG_K1_IMPL", impl)
     rng = np.random.RandomState(4000 + n)
