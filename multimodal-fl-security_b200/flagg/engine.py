@@ -300,13 +300,12 @@ class Updates:
         """Flat [d] result -> list of P tensors shaped like the inputs, on the inputs' device."""
         if to_host and flat.is_cuda:
             flat = flat.cpu()
-        out, off = [], 0
-        for p in range(self.P):
-            t = flat[off:off + self.numel[p]].reshape(self.shapes[p])
-            if dtypes is not None and dtypes[p] != t.dtype:
-                t = t.to(dtypes[p])
-            out.append(t)
-            off += self.numel[p]
+        # one split call (P views from C++), then one view() per tensor: at P = 161 the slice + reshape loop this
+        # replaces cost more than the native walk over all 16,100 input handles
+        parts = flat.split(self.numel) if self.P > 1 else (flat,)
+        out = [t.view(s) for t, s in zip(parts, self.shapes)]
+        if dtypes is not None:
+            out = [t if d == t.dtype else t.to(d) for t, d in zip(out, dtypes)]
         return out
 
 
