@@ -124,7 +124,9 @@ colselect_radix_kernel(ViewDev v, int mode, int k, float* __restrict__ out, int6
 using namespace flagg;
 
 extern "C" int flagg_colwise_select(const flagg_view* v, int mode, int k, float* out, void* stream) {
-    FLAGG_REQUIRE(v && (out || v->dev.out_ptrs), "flagg_colwise_select: NULL argument");
+    FLAGG_REQUIRE(v, "flagg_colwise_select: NULL view");
+    if (v->dev.d == 0) return FLAGG_OK;   // an empty column shard (d < 1024 x ranks): nothing to write, `out` may be NULL
+    FLAGG_REQUIRE(out || v->dev.out_ptrs, "flagg_colwise_select: NULL argument");
     FLAGG_REQUIRE(mode == FLAGG_MEDIAN || mode == FLAGG_TRIMMED_MEAN, "flagg_colwise_select: bad mode %d", mode);
     const_cast<flagg_view*>(v)->last_stream = stream;
     const int n = v->dev.n;

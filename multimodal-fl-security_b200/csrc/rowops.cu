@@ -381,6 +381,16 @@ int flagg_round_weights(int rule, int n, const double* sumsq, const double* dot,
 int flagg_row_reduce(const flagg_view* cv, const float* g0, int centered, double* sumsq, double* dot, float* linf,
                      double* g0_sumsq, void* stream) {
     FLAGG_REQUIRE(cv, "flagg_row_reduce: NULL view");
+    if (cv->dev.d == 0) {   // an empty column shard: the rank's partial statistics are zeros (g0 is an empty tensor, i.e. NULL)
+        const int n0 = cv->dev.n;
+        cudaStream_t s0 = static_cast<cudaStream_t>(stream);
+        const_cast<flagg_view*>(cv)->last_stream = stream;
+        if (sumsq) FLAGG_CUDA(cudaMemsetAsync(sumsq, 0, sizeof(double) * n0, s0));
+        if (dot) FLAGG_CUDA(cudaMemsetAsync(dot, 0, sizeof(double) * n0, s0));
+        if (linf) FLAGG_CUDA(cudaMemsetAsync(linf, 0, sizeof(float) * n0, s0));
+        if (g0_sumsq) FLAGG_CUDA(cudaMemsetAsync(g0_sumsq, 0, sizeof(double), s0));
+        return FLAGG_OK;
+    }
     FLAGG_REQUIRE(!(dot && !g0), "flagg_row_reduce: dot requested without g0");
     FLAGG_REQUIRE(!(g0_sumsq && !g0), "flagg_row_reduce: g0_sumsq requested without g0");
     FLAGG_REQUIRE(!(centered && !g0), "flagg_row_reduce: centered statistics need g0");
@@ -456,6 +466,7 @@ int flagg_row_combine(const flagg_view* cv, int m, const int32_t* rows, const fl
                       float divisor, float* out, void* stream) {
     FLAGG_REQUIRE(cv, "flagg_row_combine: NULL argument");
     flagg_view* v = const_cast<flagg_view*>(cv);
+    if (v->dev.d == 0) { v->last_stream = stream; return FLAGG_OK; }   // empty column shard: nothing to write
     FLAGG_REQUIRE(out || v->dev.out_ptrs, "flagg_row_combine: NULL output (and no flagg_view_set_outputs table)");
     v->last_stream = stream;
     const int n = v->dev.n;
@@ -483,6 +494,11 @@ int flagg_row_combine_dev(const flagg_view* cv, int m, const int32_t* d_rows, co
                           const float* d_divisor, float* out, const float* prev, double* delta_sumsq, void* stream) {
     FLAGG_REQUIRE(cv && d_divisor, "flagg_row_combine_dev: NULL argument");
     flagg_view* v = const_cast<flagg_view*>(cv);
+    if (v->dev.d == 0) {   // empty column shard: nothing to write; its share of ||out - prev||^2 is 0
+        v->last_stream = stream;
+        if (delta_sumsq) FLAGG_CUDA(cudaMemsetAsync(delta_sumsq, 0, sizeof(double), static_cast<cudaStream_t>(stream)));
+        return FLAGG_OK;
+    }
     FLAGG_REQUIRE(out || v->dev.out_ptrs, "flagg_row_combine_dev: NULL output (and no flagg_view_set_outputs table)");
     FLAGG_REQUIRE(m >= 1 && (d_rows || m == v->dev.n), "flagg_row_combine_dev: need m >= 1, and m == n when rows == NULL");
     FLAGG_REQUIRE(!delta_sumsq || prev, "flagg_row_combine_dev: delta_sumsq needs prev");

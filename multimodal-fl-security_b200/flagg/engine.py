@@ -354,7 +354,7 @@ def row_stats(u: Updates, g0_flat: Optional[torch.Tensor] = None, group=None, ce
             g0_flat = g0_flat.to(device=u.device, dtype=torch.float32).contiguous()
             if g0_flat.numel() != u.d:
                 raise ValueError("g0 has the wrong number of elements")
-            g_ptr = g0_flat.data_ptr()
+            g_ptr = g0_flat.data_ptr() or None          # empty column shard: zeros are this rank's partial sums
         p = buf.data_ptr()
         check(lib().flagg_row_reduce(u.view(), g_ptr, 1 if centered else 0, p, (p + 8 * n) if g_ptr else None, linf.data_ptr(),
                                      (p + 16 * n) if g_ptr else None, _stream()), "flagg_row_reduce")
@@ -415,12 +415,12 @@ def weighted_round(u: Updates, rule: int, num_examples=None, g0_flat: Optional[t
         st = _stream()
         buf = torch.zeros(2 * n + 1, dtype=torch.float64, device=u.device)
         linf = torch.zeros(n, dtype=torch.float32, device=u.device)
-        g_ptr = None
-        if g0_flat is not None:
+        g_ptr, has_g0 = None, g0_flat is not None
+        if has_g0:
             g0_flat = g0_flat.to(device=u.device, dtype=torch.float32).contiguous()
             if g0_flat.numel() != u.d:
                 raise ValueError("g0 has the wrong number of elements")
-            g_ptr = g0_flat.data_ptr()
+            g_ptr = g0_flat.data_ptr() or None          # an empty column shard: no pointer, the partial sums stay zero
         p = buf.data_ptr()
         check(L.flagg_row_reduce(u.view(), g_ptr, 0, p, (p + 8 * n) if g_ptr else None, linf.data_ptr(),
                                  (p + 16 * n) if g_ptr else None, st), "flagg_row_reduce")
@@ -436,8 +436,8 @@ def weighted_round(u: Updates, rule: int, num_examples=None, g0_flat: Optional[t
         info = torch.empty(n + 1, dtype=torch.float64, device=u.device)           # per-client value; the last slot holds the two counts
         keep = torch.empty(n, dtype=torch.uint8, device=u.device)
         wp = w.data_ptr()
-        check(L.flagg_round_weights(int(rule), n, None if use_linf else p, (p + 8 * n) if g_ptr else None,
-                                    (p + 16 * n) if g_ptr else None, linf.data_ptr() if use_linf else None,
+        check(L.flagg_round_weights(int(rule), n, None if use_linf else p, (p + 8 * n) if has_g0 else None,
+                                    (p + 16 * n) if has_g0 else None, linf.data_ptr() if use_linf else None,
                                     ne.data_ptr() if ne is not None else None, float(p0), float(p1), rows.data_ptr(), wp, wp + 4 * n,
                                     wp + 8 * n, info.data_ptr(), info.data_ptr() + 8 * n, keep.data_ptr(), st), "flagg_round_weights")
         out = torch.empty(u.d, dtype=torch.float32, device=u.device) if outs is None else None

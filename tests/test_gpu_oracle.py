@@ -621,6 +621,37 @@ def test_native_communicator_single_rank_and_errors():
     comm.close()
 
 
+def test_empty_column_shard_joins_every_step():
+    """A rank whose column shard is empty (d < 1024 x ranks, flagg.sharding.shard_update_lists hands it one
+    zero-length tensor per client) must run every defense to the end -- zero partial statistics into the
+    all-reduces, an empty slice out -- instead of raising and leaving the other ranks in a collective.  One rank and
+    a one-rank communicator are enough to walk every code path."""
+    from flagg import Comm
+    from src.defenses import (FLTrustDefense, GeometricMedianDefense, GradientClippingDefense, KrumDefense, MedianDefense,
+                              MultiKrumDefense, NoDefense, NormBoundingDefense, TrimmedMeanDefense, DPSGDDefense)
+
+    class Fixed(FLTrustDefense):
+        def _compute_server_gradient(self, global_params):
+            self.server_gradient = global_params
+            return global_params
+
+    comm = Comm(1, 0, Comm.unique_id())
+    for n in (12, 40):
+        ups = [[torch.zeros(0, device="cuda")] for _ in range(n)]
+        ne = [3] * n
+        cases = [(KrumDefense, {"num_malicious": 2, "multi_k": 1}, {}), (MultiKrumDefense, {"num_malicious": 2, "multi_k": 4}, {}),
+                 (MedianDefense, {}, {}), (TrimmedMeanDefense, {"trim_ratio": 0.1}, {}), (NoDefense, {}, {}),
+                 (GradientClippingDefense, {"clip_norm": 1.0}, {}), (GradientClippingDefense, {"clip_norm": 1.0, "clip_type": "linf"}, {}),
+                 (NormBoundingDefense, {"max_norm": 1.0}, {}), (DPSGDDefense, {"clip_norm": 1.0, "noise_multiplier": 0.1}, {}),
+                 (GeometricMedianDefense, {"max_iters": 5}, {}),
+                 (Fixed, {}, {"global_params": [torch.zeros(0, device="cuda")]})]
+        for cls, cfg, kw in cases:
+            res = cls(dict(cfg, process_group=comm)).aggregate(ups, ne, **kw)
+            assert sum(int(t.numel()) for t in res) == 0, cls.__name__
+    torch.cuda.synchronize()
+    comm.close()
+
+
 def test_errors_surface_as_exceptions():
     from flagg import FlaggError, TRIMMED_MEAN, engine
     from src.defenses import KrumDefense, get_defense
