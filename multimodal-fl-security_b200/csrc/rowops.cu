@@ -57,9 +57,9 @@ row_reduce_kernel(ViewDev v, const float* __restrict__ g0, double* __restrict__ 
         const int len = int(min((long long)(RR_CHUNK), (long long)segn - c0));
         __syncthreads();  // previous unit's readers of g0s are done (also orders the init above)
         if (HAS_G0) {
-            const float* gsrc = g0 + v.seg_start[p] + c0;
+            const float* gsrc = g0 ? g0 + v.seg_start[p] + c0 : nullptr;       // g0 == nullptr: zeros are staged (see the launch)
             for (int j = tid; j < RR_CHUNK; j += RR_THREADS) {
-                float g = (j < len) ? __ldg(gsrc + j) : 0.f;
+                float g = (gsrc && j < len) ? __ldg(gsrc + j) : 0.f;
                 g0s[j] = g;
                 g0ss += double(g * g);
             }
@@ -421,10 +421,13 @@ int flagg_row_reduce(const flagg_view* cv, const float* g0, int centered, double
         FLAGG_CUDA(cudaGetLastError());
         return FLAGG_OK;
     };
+    // Without g0 the vectorised kernel still runs its "with g0" form on staged zeros: the shared-memory reads between
+    // the load loop and the arithmetic keep the sixteen 128-bit loads per thread in flight (64 registers); the form
+    // compiled without them lets ptxas sink every load to its use (32 registers, ~4 in flight) and ran at 4.3 TB/s
+    // against 6.4 (profiles/r02_c5_breakdown.txt).  The wasted dot products are free under the HBM bound.
     if (vec4 && g0 && centered) rc = launch(row_reduce_kernel<true, true, true>);
     else if (g0 && centered) rc = launch(row_reduce_kernel<false, true, true>);
-    else if (vec4 && g0) rc = launch(row_reduce_kernel<true, true, false>);
-    else if (vec4) rc = launch(row_reduce_kernel<true, false, false>);
+    else if (vec4) rc = launch(row_reduce_kernel<true, true, false>);
     else if (g0) rc = launch(row_reduce_kernel<false, true, false>);
     else rc = launch(row_reduce_kernel<false, false, false>);
     if (rc != FLAGG_OK) return rc;
