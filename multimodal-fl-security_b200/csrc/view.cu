@@ -190,7 +190,9 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
         if (ok) {
             // Rows of 256 columns at a 512-byte pitch (consecutive rows overlap by half): a 256-column unit of a tensor
             // is row seg_rows + 2 * unit, and a gather4 request carries 4 KB.  The last row is kept inside the range.
-            // FLAGG_K1_GATHER_COLS=128 selects plain 128-column rows (2 KB per request; tuning / tests).
+            // Used where the networks are issue-bound (80 <= n <= 110, like the dense feed); below that 128-column
+            // rows (2 KB per request, four CTAs of 128 threads) measured 3-14 % faster, n = 32: 6.8 against 5.9 TB/s
+            // (profiles/r02_k1_layouts.txt).  FLAGG_K1_GATHER_COLS=128|256 forces one (tests, tuning).
             const char* gc = getenv("FLAGG_K1_GATHER_COLS");
             const cuuint64_t rows = cuuint64_t((hi - lo) >> 9);
             const cuuint64_t gstride[1] = {512u};
@@ -201,7 +203,8 @@ int flagg_view_create(flagg_view** out, int n, int P, const int64_t* seg_numel,
             CUresult r = encode(&gmap[1], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, reinterpret_cast<void*>(lo), gdim1, gstride, box1, estride,
                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-            if (r == CUDA_SUCCESS && !(gc && atoi(gc) == 128) && rows >= 2) {
+            const bool want_wide = gc ? atoi(gc) == 256 : (n >= 80 && n <= 110);
+            if (r == CUDA_SUCCESS && want_wide && rows >= 2) {
                 const cuuint64_t gdim2[2] = {256u, rows - 1};
                 const cuuint32_t box2[2] = {256u, 1u};
                 if (encode(&gmap[0], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, reinterpret_cast<void*>(lo), gdim2, gstride, box2, estride,
