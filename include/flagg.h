@@ -119,6 +119,20 @@ int flagg_colwise_select(const flagg_view* v, int mode, int k, float* out, void*
 int flagg_row_reduce(const flagg_view* v, const float* g0, int centered, double* sumsq,
                      double* dot, float* linf, double* g0_sumsq, void* stream);
 
+/* flagg_row_reduce for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments, same
+ * kernels, same grid and therefore the same results bit for bit; the per-CTA partial sums live in a file-scope
+ * `static __device__` array of FLAGG_STATIC_SCRATCH_BYTES (every GPU that loads libflagg.so holds it until exit)
+ * instead of the view's scratch block, and the call makes no cudaMalloc / cudaMallocAsync / cudaFree.  The view is
+ * an input: create it beforehand, on the device that is current at this call.
+ * Limit: the partials take 20 n + 8 bytes per CTA, min(ceil-units of 2048 columns, 4 x SM count) CTAs -- n <= 708
+ * clients on a 148-SM B200 at any d; beyond the array the call returns FLAGG_EUNSUPPORTED and launches nothing.
+ * Every call on a device shares the one array: calls that may overlap on the GPU (different streams, no ordering
+ * between them) race on it -- serialise them.  Nothing in it needs clearing between calls. */
+#define FLAGG_STATIC_SCRATCH_BYTES (8u << 20)
+int flagg_row_reduce_static(const flagg_view* v, const float* g0, int centered, double* sumsq,
+                            double* dot, float* linf, double* g0_sumsq, void* stream);
+
 /* ---- K3: weighted row combination ------------------------------------------ */
 /* out[c] = ( ...((0 + t_0) + t_1) ... + t_{m-1}) / divisor,
  *   t_j = w2[j] * (w1[j] * x[rows[j]][c])

@@ -7,6 +7,9 @@
 //     krum.py:187-190, fltrust.py:262-268, differential_privacy.py:148-155,262-269,325-332.
 // Both are HBM-bound streaming kernels: 128-bit coalesced loads, no shared-memory
 // staging of X (no reuse), grid sized from the SM count.
+#include <algorithm>
+#include <mutex>
+
 #include "common.cuh"
 
 namespace flagg {
@@ -522,3 +525,100 @@ int flagg_weiszfeld_weights(const double* sumsq, int n, float* w, float* wsum, v
 }
 
 }  // extern "C"
+
+// ---- K2 without any allocation (no counterpart in the reference) ----
+// flagg_row_reduce keeps its per-CTA partials in the view's scratch block, which ensure_scratch grows with
+// cudaMallocAsync.  Callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid it) get the
+// same two kernels with the partials in this file-scope array instead: FLAGG_STATIC_SCRATCH_BYTES per GPU that loads
+// the library, held until exit.  The name below is a device symbol: host code may not pass it to a kernel; its device
+// address is looked up once per device with cudaGetSymbolAddress.
+static __device__ __align__(256) unsigned char g_rr_static_scratch[FLAGG_STATIC_SCRATCH_BYTES];
+
+namespace flagg {
+
+constexpr int RRS_MAX_DEVICES = 64;
+
+// Device address of g_rr_static_scratch on the CURRENT device (each device has its own copy of the array).
+static int rr_static_scratch(unsigned char** out) {
+    static void* addr[RRS_MAX_DEVICES] = {};
+    static bool known[RRS_MAX_DEVICES] = {};
+    static std::mutex mu;
+    int dev = -1;
+    FLAGG_CUDA(cudaGetDevice(&dev));
+    FLAGG_REQUIRE(dev >= 0 && dev < RRS_MAX_DEVICES, "flagg_row_reduce_static: device ordinal %d outside 0..%d", dev, RRS_MAX_DEVICES - 1);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!known[dev]) {
+        void* p = nullptr;
+        FLAGG_CUDA(cudaGetSymbolAddress(&p, g_rr_static_scratch));
+        FLAGG_REQUIRE(p != nullptr, "flagg_row_reduce_static: cudaGetSymbolAddress returned a NULL address on device %d", dev);
+        addr[dev] = p;
+        known[dev] = true;
+    }
+    *out = static_cast<unsigned char*>(addr[dev]);
+    return FLAGG_OK;
+}
+
+}  // namespace flagg
+
+extern "C" int flagg_row_reduce_static(const flagg_view* cv, const float* g0, int centered, double* sumsq, double* dot,
+                                       float* linf, double* g0_sumsq, void* stream) {
+    FLAGG_REQUIRE(cv, "flagg_row_reduce_static: NULL view");
+    flagg_view* v = const_cast<flagg_view*>(cv);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int n = v->dev.n;
+    if (v->dev.d == 0) {   // empty column shard: zeros, as flagg_row_reduce gives
+        if (sumsq) FLAGG_CUDA(cudaMemsetAsync(sumsq, 0, sizeof(double) * n, st));
+        if (dot) FLAGG_CUDA(cudaMemsetAsync(dot, 0, sizeof(double) * n, st));
+        if (linf) FLAGG_CUDA(cudaMemsetAsync(linf, 0, sizeof(float) * n, st));
+        if (g0_sumsq) FLAGG_CUDA(cudaMemsetAsync(g0_sumsq, 0, sizeof(double), st));
+        return FLAGG_OK;
+    }
+    FLAGG_REQUIRE(!(dot && !g0), "flagg_row_reduce_static: dot requested without g0");
+    FLAGG_REQUIRE(!(g0_sumsq && !g0), "flagg_row_reduce_static: g0_sumsq requested without g0");
+    FLAGG_REQUIRE(!(centered && !g0), "flagg_row_reduce_static: centered statistics need g0");
+    int dev = -1;
+    FLAGG_CUDA(cudaGetDevice(&dev));
+    FLAGG_REQUIRE(dev == v->device, "flagg_row_reduce_static: the view was created on device %d, the current device is %d", v->device, dev);
+    v->last_stream = stream;   // the kernels read the view's tables: flagg_view_destroy orders their release after this stream
+    const int64_t units = v->total_units[GRAN_2K];
+    const size_t smem = size_t(n) * 16 + RR_CHUNK * 4 + size_t(n) * 4;
+    FLAGG_REQUIRE(smem <= 200 * 1024, "flagg_row_reduce_static: n=%d too large for the per-CTA accumulators", n);
+    const int sms = device_sm_count();
+    FLAGG_REQUIRE(sms > 0, "cannot query the SM count of the current device");
+    // the grid, the partial layout and both kernels are flagg_row_reduce's: the results are the same bit for bit
+    const int nblocks = int(std::min<int64_t>(std::max<int64_t>(units, 1), int64_t(sms) * 4));
+    const size_t b_d = sizeof(double) * size_t(nblocks) * n;
+    const size_t b_f = sizeof(float) * size_t(nblocks) * n;
+    const size_t need = 2 * b_d + ((b_f + 7) & ~size_t(7)) + sizeof(double) * nblocks;
+    if (need > size_t(FLAGG_STATIC_SCRATCH_BYTES)) {
+        set_error("flagg_row_reduce_static: %d clients x %d CTAs need %zu bytes of partial sums, the static scratch array holds "
+                  "%zu (FLAGG_STATIC_SCRATCH_BYTES); use flagg_row_reduce", n, nblocks, need, size_t(FLAGG_STATIC_SCRATCH_BYTES));
+        return FLAGG_EUNSUPPORTED;
+    }
+    unsigned char* s = nullptr;
+    int rc = rr_static_scratch(&s);
+    if (rc != FLAGG_OK) return rc;
+    // Nothing in the array has to start at zero: every CTA writes all of its n x 3 + 1 partials, and the finalize kernel
+    // reads exactly the nblocks x n entries this launch wrote -- what an earlier call left behind is never read.
+    double* part_ss = reinterpret_cast<double*>(s);
+    double* part_dot = reinterpret_cast<double*>(s + b_d);
+    double* part_g0 = reinterpret_cast<double*>(s + 2 * b_d);
+    float* part_linf = reinterpret_cast<float*>(s + 2 * b_d + sizeof(double) * nblocks);
+    const bool vec4 = v->align_bytes >= 16;
+    auto launch = [&](auto kern) -> int {
+        FLAGG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        kern<<<nblocks, RR_THREADS, smem, st>>>(v->dev, g0, part_ss, part_dot, part_linf, part_g0, units);
+        FLAGG_CUDA(cudaGetLastError());
+        return FLAGG_OK;
+    };
+    if (vec4 && g0 && centered) rc = launch(row_reduce_kernel<true, true, true>);
+    else if (g0 && centered) rc = launch(row_reduce_kernel<false, true, true>);
+    else if (vec4) rc = launch(row_reduce_kernel<true, true, false>);      // g0 == NULL: staged zeros, see flagg_row_reduce
+    else if (g0) rc = launch(row_reduce_kernel<false, true, false>);
+    else rc = launch(row_reduce_kernel<false, false, false>);
+    if (rc != FLAGG_OK) return rc;
+    row_reduce_finalize<<<(n + 127) / 128, 128, 0, st>>>(part_ss, part_dot, part_linf, part_g0, nblocks, n,
+                                                         sumsq, dot, linf, g0_sumsq);
+    FLAGG_CUDA(cudaGetLastError());
+    return FLAGG_OK;
+}

@@ -11,6 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FLAGG_LIB") or os.path.join(_HERE, "libflagg.so")   # FLAGG_LIB: tuning builds only
 
 MEDIAN, TRIMMED_MEAN = 0, 1
+STATIC_SCRATCH_BYTES = 8 << 20          # FLAGG_STATIC_SCRATCH_BYTES (flagg_row_reduce_static)
 T_SCALE, T_REPLACE, T_SIGN, T_AXPY = 0, 1, 2, 3
 
 
@@ -42,6 +43,7 @@ def lib():
         "flagg_view_rows": (i32, [vp]),
         "flagg_colwise_select": (i32, [vp, i32, i32, vp, vp]),
         "flagg_row_reduce": (i32, [vp, vp, i32, vp, vp, vp, vp, vp]),
+        "flagg_row_reduce_static": (i32, [vp, vp, i32, vp, vp, vp, vp, vp]),
         "flagg_row_combine": (i32, [vp, i32, C.POINTER(C.c_int32), C.POINTER(f32), C.POINTER(f32), f32, vp, vp]),
         "flagg_row_combine_dev": (i32, [vp, i32, vp, vp, vp, vp, vp, vp, vp, vp]),
         "flagg_weiszfeld_weights": (i32, [vp, i32, vp, vp, vp]),
@@ -76,7 +78,7 @@ EXPORTS = ["flagg_version", "flagg_last_error", "flagg_device_info", "flagg_view
            "flagg_sqdist", "flagg_krum_scores_from_sqdist", "flagg_round_weights", "flagg_view_cols", "flagg_view_rows", "flagg_colwise_select", "flagg_row_reduce", "flagg_row_combine",
            "flagg_gram", "flagg_krum_scores", "flagg_colwise_select_host", "flagg_upload_rows", "flagg_host_release", "flagg_comm_unique_id",
            "flagg_comm_create", "flagg_comm_destroy", "flagg_comm_size", "flagg_comm_rank", "flagg_allreduce_f64",
-           "flagg_allreduce_f32", "flagg_comm_scatter_columns"]
+           "flagg_allreduce_f32", "flagg_comm_scatter_columns", "flagg_row_reduce_static"]
 
 
 def check(rc: int, what: str) -> None:
