@@ -23,7 +23,10 @@ namespace flagg {
 int gram_tc_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st);  // gram_tc.cu
 int gram_small_launch(flagg_view* v, const float* center, int accumulate, double* G, cudaStream_t st);  // gram_small.cu (n <= 32)
 int sqdist_small_launch(flagg_view* v, int accumulate, double* D2, cudaStream_t st);                          // sqdist_small.cu (n <= 32)
+int sqdist_pairs_launch(flagg_view* v, int accumulate, double* D2, cudaStream_t st);                          // sqdist_pairs.cu (16-byte aligned rows)
+bool sqdist_pairs_serves(int n);
 
+constexpr int SQDIST_PAIRS_MIN_N = 9;   // flagg_sqdist: pair-group kernel from this cohort size (profiles/r02_krum_small_sqdist.txt)
 constexpr int GT = 64;          // output tile edge
 constexpr int GK = 32;          // columns per k-step (128 B of every row)
 constexpr int G_THREADS = 256;  // 16 x 16 threads, 4 x 4 outputs each
@@ -274,7 +277,29 @@ int flagg_sqdist(const flagg_view* cv, int accumulate, double* D2, void* stream)
         set_error("flagg_sqdist: serves cohorts of up to 32 clients (n=%d); larger cohorts use flagg_gram", v->dev.n);
         return FLAGG_EUNSUPPORTED;
     }
-    return sqdist_small_launch(v, accumulate, D2, static_cast<cudaStream_t>(stream));
+    // Two kernels, the same arithmetic per pair and column: pair groups (sqdist_pairs.cu: every warp the same work, rows
+    // by 512-byte bulk copies) for 16-byte aligned rows from SQDIST_PAIRS_MIN_N clients, row-block jobs (sqdist_small.cu)
+    // otherwise.  FLAGG_SQDIST_IMPL=pairs|jobs forces one (tests, tuning).
+    const int64_t units = v->total_units[GRAN_128];
+    const bool pairs_ok = sqdist_pairs_serves(v->dev.n) && v->align_bytes >= 16 && units >= 1 && units < (int64_t(1) << 24);
+    const char* impl = getenv("FLAGG_SQDIST_IMPL");
+    bool pairs = pairs_ok && v->dev.n >= SQDIST_PAIRS_MIN_N;
+    if (impl && *impl) {
+        if (!strcmp(impl, "pairs")) {
+            if (!pairs_ok) {
+                set_error("FLAGG_SQDIST_IMPL=pairs: needs 2 <= n <= 29, 16-byte aligned rows and fewer than 2^31 columns");
+                return FLAGG_EUNSUPPORTED;
+            }
+            pairs = true;
+        } else if (!strcmp(impl, "jobs")) {
+            pairs = false;
+        } else {
+            set_error("FLAGG_SQDIST_IMPL=%s: expected pairs or jobs", impl);
+            return FLAGG_EINVAL;
+        }
+    }
+    return pairs ? sqdist_pairs_launch(v, accumulate, D2, static_cast<cudaStream_t>(stream))
+                 : sqdist_small_launch(v, accumulate, D2, static_cast<cudaStream_t>(stream));
 }
 
 int flagg_krum_scores_from_sqdist(const double* D2, int n, int f, double* D, double* scores, void* stream) {

@@ -380,29 +380,44 @@ def test_gram_small_cohorts_vs_fp64(n, seg, f, impl, monkeypatch):
     u.close()
 
 
-@pytest.mark.parametrize("aligned", [True, False])
+@pytest.mark.parametrize("aligned", [True, False, "dense", "offset16"])
 @pytest.mark.parametrize("n,seg,f", [(2, [300], 0), (3, [4096], 0), (4, [4096], 0), (8, [777, 33], 2), (9, [5000, 1, 260], 2),
                                      (10, [288, 32, 18432, 64, 401408, 128, 1280, 10], 2), (16, [3000], 4), (17, [64, 2050], 4),
                                      (20, [130000, 36], 5), (24, [50000], 6), (25, [4100, 95], 6), (31, [700, 3], 8), (32, [9000, 31], 8)])
-def test_sqdist_small_cohorts_vs_fp64(n, seg, f, aligned):
+@pytest.mark.parametrize("impl", ["default", "jobs", "pairs"])
+def test_sqdist_small_cohorts_vs_fp64(n, seg, f, aligned, impl, monkeypatch):
     """flagg_sqdist (the reference's default cohort sizes, n <= 32): squared distances by direct
-    differences with packed fp32x2 arithmetic, every job layout (1 / 2 / 3 / 4 row blocks), 128-bit
-    and 4-byte copies, ragged tensors.  Distances within 1e-5 of FP64 (measured ~1e-7), exact
-    symmetry and zero diagonal, exactly 0 between duplicate rows, Krum ranking as FP64's, repeatable
-    bit for bit, accumulate=1 adds."""
+    differences, both kernels (row-block jobs: every job layout, 1 / 2 / 3 / 4 row blocks, 128-bit and
+    4-byte copies; pair groups: 1-5 groups, bulk copies and the ragged-unit path), ragged tensors.
+    Distances within 1e-5 of FP64 (measured ~1e-7), exact symmetry and zero diagonal, exactly 0
+    between duplicate rows, Krum ranking as FP64's, repeatable bit for bit, accumulate=1 adds."""
     from flagg import engine
     from flagg._lib import check, lib
+    if impl == "pairs" and (not aligned or n > 29):
+        pytest.skip("the pair-group kernel needs 16-byte aligned rows and serves up to 29 clients")
+    if impl != "default":
+        monkeypatch.setenv("FLAGG_SQDIST_IMPL", impl)
     d = sum(seg)
     rng = np.random.RandomState(n + d)
     X = rows_model(rng, n, d, byz=f)
     if n > 2:
         X[1] = X[0]
-    if aligned:
+    offs = np.concatenate([[0], np.cumsum(seg)]).astype(int)
+    if aligned is True:                                                # separately allocated tensors: tile::gather4 feed
         ups = dev_lists(X, seg)
+    elif aligned == "dense":                                           # rows of one matrix per tensor: 2-D box feed
+        mats = [torch.from_numpy(np.ascontiguousarray(np.pad(X[:, offs[p]:offs[p + 1]], ((0, 0), (0, (-seg[p]) % 4)))).astype(np.float32)).cuda()
+                for p in range(len(seg))]
+        ups = [[mats[p][i, :seg[p]] for p in range(len(seg))] for i in range(n)]
+    elif aligned == "offset16":                                        # 16-byte but not 512-byte aligned rows: per-row bulk copies
+        bufs = [[torch.zeros(seg[p] + 4, device="cuda") for p in range(len(seg))] for _ in range(n)]
+        ups = [[bufs[i][p][4:] for p in range(len(seg))] for i in range(n)]
+        for i in range(n):
+            for p in range(len(seg)):
+                ups[i][p].copy_(torch.from_numpy(X[i, offs[p]:offs[p + 1]]))
     else:                                                              # 4-byte aligned views into one buffer
         big = torch.zeros((n, d + 1), device="cuda")
         big[:, 1:] = torch.from_numpy(X).cuda()
-        offs = np.concatenate([[0], np.cumsum(seg)]).astype(int)
         ups = [[big[i, 1 + offs[p]:1 + offs[p + 1]] for p in range(len(seg))] for i in range(n)]
     u = engine.Updates(ups)
     D2 = engine.sqdist(u)
@@ -425,10 +440,12 @@ def test_sqdist_small_cohorts_vs_fp64(n, seg, f, aligned):
     u.close()
 
 
-def test_sqdist_nonfinite_rows_follow_ieee_like_torch_norm():
+@pytest.mark.parametrize("impl", ["jobs", "pairs"])
+def test_sqdist_nonfinite_rows_follow_ieee_like_torch_norm(impl, monkeypatch):
     """A NaN client, an Inf client and a pair of Inf clients: flagg_sqdist gives NaN / inf exactly
     where the reference's torch.norm(f_i - f_j) does (krum.py:95), no special path involved."""
     from flagg import engine
+    monkeypatch.setenv("FLAGG_SQDIST_IMPL", impl)
     rng = np.random.RandomState(3)
     n, d = 14, 3000
     X = rows_model(rng, n, d)

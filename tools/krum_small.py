@@ -31,13 +31,19 @@ for n in ns:
     X = torch.randn((n, d), device="cuda") * 1e-3 + 0.05
     ups = [[torch.empty(d, device="cuda").copy_(X[i])] for i in range(n)]
     u = engine.Updates(ups)
+    t_impl = {}
+    for impl in ("jobs", "pairs"):
+        os.environ["FLAGG_SQDIST_IMPL"] = impl
+        ref = engine.sqdist(u)
+        t_impl[impl] = timed(lambda: engine.sqdist(u))
+    del os.environ["FLAGG_SQDIST_IMPL"]
     t_sq = timed(lambda: engine.sqdist(u))
     t_gram = timed(lambda: engine.gram(u))
     f = max(0, (n - 3) // 4)
     k = KrumDefense({"num_malicious": f, "multi_k": 1})
     t_api = timed(lambda: k.aggregate(ups, [1] * n)) if n >= 2 * f + 3 else float("nan")
     gb = 4.0 * n * d / 1e6
-    print(f"n={n:2d} d={d} sqdist {t_sq:6.3f} ms = {gb / t_sq:6.0f} GB/s | centre + Gram {t_gram:6.3f} ms | "
+    print(f"n={n:2d} d={d} sqdist {t_sq:6.3f} ms = {gb / t_sq:6.0f} GB/s (jobs {t_impl['jobs']:6.3f}, pairs {t_impl['pairs']:6.3f}) | centre + Gram {t_gram:6.3f} ms | "
           f"KrumDefense.aggregate {t_api:6.3f} ms = {gb / t_api:6.0f} GB/s", flush=True)
     u.close()
     del X, ups, u
