@@ -8,10 +8,10 @@
 // accumulators in registers, lane = column) and computes it for a whole 32-column quarter at a time from N
 // shared-memory loads.  Every warp of the kernel executes the same instruction count per quarter, so the barrier that
 // closes a stage finds the warps together, and there are N loads per 2 G arithmetic instructions instead of 12 per 64.
-//     CTA = H x CS warps (CS column slots; 3-6 warps), one 128-column unit per stage, CTA-private ring filled by 512-byte bulk copies (TMA engine);
-//     registers capped at 168 -> 12 warps per SM; units dealt round-robin over the grid (neighbouring columns are
-//     read at the same time); fp32 accumulation over at most 1024 columns per lane, FP64 across lanes, per-warp
-//     partials, fixed-order reduce (deterministic).
+//     H = 1, 2 or 4 groups; CTA = 2 or 4 warps, one 128-column unit per stage, CTA-private ring filled by the TMA
+//     engine (2-D box, tile::gather4 or per-row bulk copies, see the loader); registers capped at 168 -> 12 warps per
+//     SM; units dealt round-robin over the grid (neighbouring columns are read at the same time); fp32 accumulation
+//     over at most 1024 columns per lane, FP64 across lanes, per-warp partials, fixed-order reduce (deterministic).
 // Arithmetic per pair and column is the same as in sqdist_small.cu: one fp32 subtraction, one fma.
 #include <algorithm>
 #include <cstdlib>
@@ -42,9 +42,12 @@ __host__ __device__ constexpr int sp_groups(int n) {
 }
 __host__ __device__ constexpr bool sp_serves(int n) { return n >= SP_MIN_N && n <= SP_MAX_N && sp_groups(n) <= SP_MAX_GROUPS; }
 __host__ __device__ constexpr int sp_group_size(int n) { return (sp_pairs(n) + sp_groups(n) - 1) / sp_groups(n); }
-// column slots per CTA: every warp computes at least two 32-column quarters per stage (with one quarter per warp and stage
-// the per-stage bookkeeping was as large as the arithmetic: n = 14 ran at 3.4 TB/s with 4 slots, 4.7 with 2)
-__host__ __device__ constexpr int sp_cslots(int h) { return h <= 2 ? 2 : 1; }
+// Column slots per CTA.  Small CTAs win: the per-stage bookkeeping (mbarrier wait, CTA barrier, ring indices, ~95
+// instructions) is paid per warp and stage, and the CTA barrier waits for the slowest of its warps.  One group: two warps
+// of two quarters each (with four warps of one quarter the bookkeeping was as large as the arithmetic: n = 14 ran at
+// 3.4 TB/s, 4.2 this way); two and four groups: one warp per group, four quarters each (n = 20: 0.270 -> 0.238 ms
+// against two slots per group).
+__host__ __device__ constexpr int sp_cslots(int h) { return h == 1 ? 2 : 1; }
 __host__ __device__ constexpr int sp_pair_index(int n, int i, int j) { return i * n - i * (i + 1) / 2 + (j - i - 1); }   // i < j
 __host__ __device__ constexpr int sp_min_blocks(int threads) { return 65536 / (threads * SP_REG_CAP) > 0 ? 65536 / (threads * SP_REG_CAP) : 1; }
 __host__ __device__ constexpr int sp_threads(int n) { return 32 * sp_groups(n) * sp_cslots(sp_groups(n)); }
@@ -114,6 +117,7 @@ __device__ __forceinline__ void sp_step(float (&acc)[sp_group_size(N)], const fl
 template <int N, int HI>
 __device__ __forceinline__ void sp_run(const ViewDev& v, int total_units, double* __restrict__ part, float* smem, uint32_t bars) {
     constexpr int H = sp_groups(N), CS = sp_cslots(H), WP = H * CS, G = sp_group_size(N), QW = 4 / CS, STAGES = sp_stages(N);
+    constexpr int QU = QW <= 2 ? QW : 1;                           // four quarters: a loop, not four copies (instruction cache)
     constexpr int NPAD = sp_npad(N), UNIT = NPAD * 128;            // floats per stage: one 128-column unit of every row
     constexpr int ROWS = (N + WP - 1) / WP;                        // rows a warp copies
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cs = warp / H;
@@ -226,9 +230,9 @@ __device__ __forceinline__ void sp_run(const ViewDev& v, int total_units, double
         __syncthreads();                                           // every warp is done with stage k - 1 (and has its ragged stores out)
         copy();
         const float* ub = smem + drain * UNIT + lane;
-        // four quarters per warp (three and more pair groups): a loop, not four copies -- the H groups run different
-        // code, and 5 x 4 x 6 KB of straight-line arithmetic fell out of the instruction cache (2.3 ms at n = 32)
-#pragma unroll(QW <= 2 ? QW : 1)
+        // four quarters per warp: a loop, not four copies -- the H groups run different code, and 5 groups x 4 x 6 KB of
+        // straight-line arithmetic fell out of the instruction cache (2.3 ms at n = 32 in an early version)
+#pragma unroll(QU)
         for (int q = 0; q < QW; ++q) sp_step<N, HI>(acc, ub + 32 * (cs * QW + q));
         if (++drain == STAGES) {
             drain = 0;
