@@ -498,13 +498,15 @@ def krum_scores(G: torch.Tensor, f: int, want_D: bool = True, want_scores: bool 
     Gram matrix, or with ``squared`` the squared distances of ``sqdist``."""
     n = G.shape[0]
     with torch.cuda.device(G.device):
-        scores = torch.empty(n, dtype=torch.float64, device=G.device) if want_scores else None
-        D = torch.empty((n, n), dtype=torch.float64, device=G.device) if want_D else None
+        # one device buffer and one read-back (one synchronisation) for both results
+        nd = n * n if want_D else 0
+        buf = torch.empty(nd + (n if want_scores else 0), dtype=torch.float64, device=G.device)
+        p = buf.data_ptr()
         fn, name = (lib().flagg_krum_scores_from_sqdist, "flagg_krum_scores_from_sqdist") if squared else \
             (lib().flagg_krum_scores, "flagg_krum_scores")
-        check(fn(G.data_ptr(), n, f, D.data_ptr() if want_D else None,
-                 scores.data_ptr() if want_scores else None, _stream()), name)
-        return (D.cpu().numpy() if want_D else None), (scores.cpu().numpy() if want_scores else None)
+        check(fn(G.data_ptr(), n, f, p if want_D else None, (p + 8 * nd) if want_scores else None, _stream()), name)
+        h = buf.cpu().numpy()
+        return (h[:nd].reshape(n, n) if want_D else None), (h[nd:] if want_scores else None)
 
 
 SMALL_COHORT = 32   # up to here distances come from direct differences (flagg_sqdist): one read of X, no centre

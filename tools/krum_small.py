@@ -34,8 +34,11 @@ for n in ns:
     t_impl = {}
     for impl in ("jobs", "pairs"):
         os.environ["FLAGG_SQDIST_IMPL"] = impl
-        ref = engine.sqdist(u)
-        t_impl[impl] = timed(lambda: engine.sqdist(u))
+        try:
+            engine.sqdist(u)
+            t_impl[impl] = timed(lambda: engine.sqdist(u))
+        except engine.FlaggError:              # the pair-group kernel serves 2..29 clients
+            t_impl[impl] = float("nan")
     del os.environ["FLAGG_SQDIST_IMPL"]
     t_sq = timed(lambda: engine.sqdist(u))
     t_gram = timed(lambda: engine.gram(u))
