@@ -26,7 +26,7 @@ int sqdist_small_launch(flagg_view* v, int accumulate, double* D2, cudaStream_t 
 int sqdist_pairs_launch(flagg_view* v, int accumulate, double* D2, cudaStream_t st);                          // sqdist_pairs.cu (16-byte aligned rows)
 bool sqdist_pairs_serves(int n);
 
-constexpr int SQDIST_PAIRS_MIN_N = 9;   // flagg_sqdist: pair-group kernel from this cohort size (profiles/r02_krum_small_sqdist.txt)
+constexpr int SQDIST_PAIRS_MIN_N = 2;   // flagg_sqdist: pair-group kernel from this cohort size (faster at every n it serves, profiles/r02_krum_small_pairs.txt)
 constexpr int GT = 64;          // output tile edge
 constexpr int GK = 32;          // columns per k-step (128 B of every row)
 constexpr int G_THREADS = 256;  // 16 x 16 threads, 4 x 4 outputs each
@@ -287,7 +287,7 @@ int flagg_sqdist(const flagg_view* cv, int accumulate, double* D2, void* stream)
     if (impl && *impl) {
         if (!strcmp(impl, "pairs")) {
             if (!pairs_ok) {
-                set_error("FLAGG_SQDIST_IMPL=pairs: needs 2 <= n <= 29, 16-byte aligned rows and fewer than 2^31 columns");
+                set_error("FLAGG_SQDIST_IMPL=pairs: needs 2 <= n <= 32, 16-byte aligned rows and fewer than 2^31 columns");
                 return FLAGG_EUNSUPPORTED;
             }
             pairs = true;

@@ -35,8 +35,11 @@ __host__ __device__ constexpr int sp_pairs(int n) { return n * (n - 1) / 2; }
 // groups, so that the warps a scheduler holds (warp id mod 4) all run the code of ONE group -- with 3, 5 or 6 groups
 // the schedulers interleave different instruction streams and the kernel starves on instruction fetch (n = 32 with
 // five groups: 0.93 ms against 0.66 for the row-block kernel).  More than 4 groups: not served (sp_serves).
+// registers per thread the kernel is built for: 168 (12 warps per SM) up to 29 clients; 30-32 clients would need 8 groups
+// there, so they get 4 groups of up to 124 accumulators in ~200 registers (8 warps per SM)
+__host__ __device__ constexpr int sp_reg_cap(int n) { return n >= 30 ? 200 : SP_REG_CAP; }
 __host__ __device__ constexpr int sp_groups(int n) {
-    const int gmax = SP_REG_CAP - n - 36;
+    const int gmax = sp_reg_cap(n) - n - 36;
     const int h = sp_pairs(n) <= gmax ? 1 : (sp_pairs(n) + gmax - 1) / gmax;
     return h <= 2 ? h : (h <= 4 ? 4 : 8);
 }
@@ -49,12 +52,12 @@ __host__ __device__ constexpr int sp_group_size(int n) { return (sp_pairs(n) + s
 // against two slots per group).
 __host__ __device__ constexpr int sp_cslots(int h) { return h == 1 ? 2 : 1; }
 __host__ __device__ constexpr int sp_pair_index(int n, int i, int j) { return i * n - i * (i + 1) / 2 + (j - i - 1); }   // i < j
-__host__ __device__ constexpr int sp_min_blocks(int threads) { return 65536 / (threads * SP_REG_CAP) > 0 ? 65536 / (threads * SP_REG_CAP) : 1; }
+__host__ __device__ constexpr int sp_min_blocks(int threads, int cap = SP_REG_CAP) { return 65536 / (threads * cap) > 0 ? 65536 / (threads * cap) : 1; }
 __host__ __device__ constexpr int sp_threads(int n) { return 32 * sp_groups(n) * sp_cslots(sp_groups(n)); }
 __host__ __device__ constexpr int sp_npad(int n) { return (n + 3) & ~3; }     // tile rows: gather4 brings four rows per request
 // ring depth: the CTAs the register cap allows per SM share 216 KB of shared memory (1 KB per CTA is the system's)
 __host__ __device__ constexpr int sp_stages(int n) {
-    const int s = (216 * 1024 / sp_min_blocks(sp_threads(n)) - 1024) / (sp_npad(n) * 512);
+    const int s = (216 * 1024 / sp_min_blocks(sp_threads(n), sp_reg_cap(n)) - 1024) / (sp_npad(n) * 512);
     return s > SP_MAX_STAGES ? SP_MAX_STAGES : (s < 2 ? 2 : s);
 }
 
@@ -239,20 +242,32 @@ __device__ __forceinline__ void sp_run(const ViewDev& v, int total_units, double
             phase ^= 1;
         }
     }
-    // lanes -> one FP64 value per accumulator (butterfly: every lane ends with the same sum)
+    // Lanes -> one FP64 value per accumulator, through shared memory (the ring is idle now): 32 accumulators at a time,
+    // every lane writes its 32 values as a column of a [32][33] tile, lane l then adds row l (accumulator 32 b + l over
+    // the 32 lanes, FP64, lane order) and the warp stores 32 sums as one 256-byte run of ITS G partials.  Small code on
+    // purpose: a fully unrolled shuffle butterfly per accumulator is ~2400 instructions per group, which pushes the hot
+    // loops of the H groups tens of KB apart -- their relative placement then decided the instruction-cache behaviour
+    // (n = 28: 0.49 or 0.55 ms depending on unrelated changes to this epilogue).
+    __syncthreads();                                               // every warp is done reading the ring
+    float* tile = smem + warp * (32 * 33);
     double* dst = part + (size_t(blockIdx.x) * WP + warp) * G;
 #pragma unroll
-    for (int e = 0; e < G; ++e) {
-        double s = double(acc[e]);
+    for (int b = 0; b < (G + 31) / 32; ++b) {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        if (lane == 0) dst[e] = s;
+        for (int i = 0; i < 32; ++i)
+            if (32 * b + i < G) tile[i * 33 + lane] = acc[32 * b + i];
+        __syncwarp();
+        double s = 0.0;
+#pragma unroll 1
+        for (int l = 0; l < 32; ++l) s += double(tile[lane * 33 + l]);
+        if (32 * b + lane < G) dst[32 * b + lane] = s;
+        __syncwarp();
     }
 }
 
 // part[((cta * WP) + warp) * G + e], warp = cs * H + group
 template <int N>
-__global__ void __launch_bounds__(sp_threads(N), sp_min_blocks(sp_threads(N)))
+__global__ void __launch_bounds__(sp_threads(N), sp_min_blocks(sp_threads(N), sp_reg_cap(N)))
 sqdist_pairs_kernel(ViewDev v, int total_units, double* __restrict__ part) {
     extern __shared__ __align__(128) float sp_smem[];
     __shared__ __align__(8) unsigned long long sp_bars[SP_MAX_STAGES];
@@ -272,36 +287,45 @@ sqdist_pairs_kernel(ViewDev v, int total_units, double* __restrict__ part) {
     static_assert(H <= SP_MAX_GROUPS, "sqdist_pairs_kernel: more pair groups than the dispatch handles");
 }
 
-// One warp per output element (r < c): lanes stride over the (cta, column slot) partials, then a fixed-shape shuffle
-// tree -- the same order every run.  The diagonal is exactly 0.
-__global__ void __launch_bounds__(256)
-sqdist_pairs_reduce_kernel(const double* __restrict__ part, int ctas, int n, int H, int CS, int G, int accumulate,
+// One CTA per pair (r < c): 128 threads stride over the pair's (cta, column slot) partials, then a
+// fixed-shape shuffle tree and a fixed-order sum over the four warps -- the same order every run.  (One WARP per pair
+// walked 28-55 dependent L2 round trips: 15-25 us of a 100-240 us call.)  The last CTA writes the exact-zero diagonal.
+constexpr int SP_REDUCE_THREADS = 128;
+__global__ void __launch_bounds__(SP_REDUCE_THREADS)
+sqdist_pairs_reduce_kernel(const double* __restrict__ part, int terms, int n, int H, int CS, int G, int accumulate,
                            double* __restrict__ D2) {
-    const int lane = threadIdx.x & 31;
-    const int el = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (el >= n * n) return;
-    const int r = el / n, c = el % n;
-    if (c < r) return;
-    if (r == c) {
-        if (lane == 0 && !accumulate) D2[size_t(r) * n + c] = 0.0;
+    __shared__ double wsum[SP_REDUCE_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, np = sp_pairs(n);
+    const int e = blockIdx.x;
+    if (e >= np) {
+        if (!accumulate)
+            for (int i = tid; i < n; i += SP_REDUCE_THREADS) D2[size_t(i) * n + i] = 0.0;
         return;
     }
-    const int e = sp_pair_index(n, r, c), h = e / G, eg = e - h * G, WP = H * CS;
-    const int terms = ctas * CS;
-    double s = 0.0;
-    for (int k = lane; k < terms; k += 32) {
-        const int cta = k / CS, cs = k % CS;
-        s += part[(size_t(cta) * WP + cs * H + h) * G + eg];
+    int r = 0, rem = e;                                            // row-major pair index -> (r, c)
+    while (rem >= n - 1 - r) {
+        rem -= n - 1 - r;
+        ++r;
     }
+    const int c = r + 1 + rem;
+    double s = 0.0;
+    const int h = e / G, eg = e - h * G, WP = H * CS;
+#pragma unroll 4
+    for (int k = tid; k < terms; k += SP_REDUCE_THREADS) s += part[(size_t(k / CS) * WP + (k % CS) * H + h) * G + eg];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) {
+    if (lane == 0) wsum[tid >> 5] = s;
+    __syncthreads();
+    if (tid == 0) {
+        double t = wsum[0];
+#pragma unroll
+        for (int w = 1; w < SP_REDUCE_THREADS / 32; ++w) t += wsum[w];
         if (accumulate) {
-            D2[size_t(r) * n + c] += s;
-            D2[size_t(c) * n + r] += s;
+            D2[size_t(r) * n + c] += t;
+            D2[size_t(c) * n + r] += t;
         } else {
-            D2[size_t(r) * n + c] = s;
-            D2[size_t(c) * n + r] = s;
+            D2[size_t(r) * n + c] = t;
+            D2[size_t(c) * n + r] = t;
         }
     }
 }
@@ -341,7 +365,7 @@ static int sp_go(flagg_view* v, int accumulate, double* D2, cudaStream_t st) {
     double* part = static_cast<double*>(v->d_scratch);
     kern<<<unsigned(ctas), T, smem, st>>>(v->dev, int(units), part);
     FLAGG_CUDA(cudaGetLastError());
-    sqdist_pairs_reduce_kernel<<<(N * N + 7) / 8, 256, 0, st>>>(part, int(ctas), N, H, CS, G, accumulate, D2);
+    sqdist_pairs_reduce_kernel<<<sp_pairs(N) + 1, SP_REDUCE_THREADS, 0, st>>>(part, int(ctas) * CS, N, H, CS, G, accumulate, D2);
     FLAGG_CUDA(cudaGetLastError());
     return FLAGG_OK;
   }

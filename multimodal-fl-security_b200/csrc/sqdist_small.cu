@@ -291,37 +291,49 @@ sqdist_small_kernel(ViewDev v, int total_units, int units_per_cta, double* __res
     }
 }
 
-// One warp per output element (r < c): lanes stride over the (cta, slot) partials, then a fixed-shape
-// shuffle tree -- the same order every run.  The diagonal is exactly 0.
-__global__ void __launch_bounds__(256)
+// One CTA per pair (r < c): 128 threads stride over the (cta, slot) partials, then a fixed-shape shuffle tree and a
+// fixed-order sum over the four warps -- the same order every run.  The last CTA writes the exact-zero diagonal.
+constexpr int SD_REDUCE_THREADS = 128;
+__global__ void __launch_bounds__(SD_REDUCE_THREADS)
 sqdist_reduce_kernel(const double* __restrict__ part, int ctas, int n, int accumulate, double* __restrict__ D2) {
+    __shared__ double wsum[SD_REDUCE_THREADS / 32];
     const int nblk = sd_nblk(n), njobs = sd_njobs(nblk), cs = SD_WARPS / njobs;
-    const int lane = threadIdx.x & 31;
-    const int el = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (el >= n * n) return;
-    const int r = el / n, c = el % n;
-    if (c < r) return;
-    if (r == c) {
-        if (lane == 0 && !accumulate) D2[size_t(r) * n + c] = 0.0;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int el = blockIdx.x, np = n * (n - 1) / 2;
+    if (el >= np) {
+        if (!accumulate)
+            for (int i = tid; i < n; i += SD_REDUCE_THREADS) D2[size_t(i) * n + i] = 0.0;
         return;
     }
+    int r = 0, rem = el;                                           // row-major pair index -> (r, c)
+    while (rem >= n - 1 - r) {
+        rem -= n - 1 - r;
+        ++r;
+    }
+    const int c = r + 1 + rem;
     int job, e;
     sd_locate(nblk, n, r, c, job, e);
     const int terms = ctas * cs;
     double s = 0.0;
-    for (int k = lane; k < terms; k += 32) {
+#pragma unroll 4
+    for (int k = tid; k < terms; k += SD_REDUCE_THREADS) {
         const int cta = k / cs, slot = k % cs;
         s += part[(size_t(cta) * SD_WARPS + slot * njobs + job) * SD_ACC + e];
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) {
+    if (lane == 0) wsum[tid >> 5] = s;
+    __syncthreads();
+    if (tid == 0) {
+        double t = wsum[0];
+#pragma unroll
+        for (int w = 1; w < SD_REDUCE_THREADS / 32; ++w) t += wsum[w];
         if (accumulate) {
-            D2[size_t(r) * n + c] += s;
-            D2[size_t(c) * n + r] += s;
+            D2[size_t(r) * n + c] += t;
+            D2[size_t(c) * n + r] += t;
         } else {
-            D2[size_t(r) * n + c] = s;
-            D2[size_t(c) * n + r] = s;
+            D2[size_t(r) * n + c] = t;
+            D2[size_t(c) * n + r] = t;
         }
     }
 }
@@ -370,8 +382,7 @@ int sqdist_small_launch(flagg_view* v, int accumulate, double* D2, cudaStream_t 
     else lrc = vec ? go(sqdist_small_kernel<true, 3, 2>) : go(sqdist_small_kernel<false, 3, 2>);
     if (lrc != FLAGG_OK) return lrc;
     FLAGG_CUDA(cudaGetLastError());
-    const int warps_per_block = 8;
-    sqdist_reduce_kernel<<<(n * n + warps_per_block - 1) / warps_per_block, 32 * warps_per_block, 0, st>>>(part, int(ctas), n, accumulate, D2);
+    sqdist_reduce_kernel<<<n * (n - 1) / 2 + 1, SD_REDUCE_THREADS, 0, st>>>(part, int(ctas), n, accumulate, D2);
     FLAGG_CUDA(cudaGetLastError());
     return FLAGG_OK;
 }

@@ -413,38 +413,45 @@ def weighted_round(u: Updates, rule: int, num_examples=None, g0_flat: Optional[t
     L = lib()
     with torch.cuda.device(u.device):
         st = _stream()
-        buf = torch.zeros(2 * n + 1, dtype=torch.float64, device=u.device)
-        linf = torch.zeros(n, dtype=torch.float32, device=u.device)
         g_ptr, has_g0 = None, g0_flat is not None
         if has_g0:
             g0_flat = g0_flat.to(device=u.device, dtype=torch.float32).contiguous()
             if g0_flat.numel() != u.d:
                 raise ValueError("g0 has the wrong number of elements")
             g_ptr = g0_flat.data_ptr() or None          # an empty column shard: no pointer, the partial sums stay zero
-        p = buf.data_ptr()
-        check(L.flagg_row_reduce(u.view(), g_ptr, 0, p, (p + 8 * n) if g_ptr else None, linf.data_ptr(),
+        # one allocation for every small device array of the round (at C1 / C2 sizes a call is host-bound: each
+        # torch.empty / torch.zeros is 5-10 us):  FP64 [2n+1] statistics | FP64 [n+1] info + counts | fp32 [n] linf |
+        # fp32 [2n+1] w1, w2, divisor | int32 [n] rows | n bytes keep
+        nbytes = 8 * (2 * n + 1) + 8 * (n + 1) + 4 * n + 4 * (2 * n + 1) + 4 * n + n
+        scratch = torch.empty(nbytes + 8, dtype=torch.uint8, device=u.device)
+        if has_g0 and g_ptr is None:
+            scratch.zero_()                             # K2 leaves dot / g0_sumsq unwritten without a g0 pointer; they are all-reduced below
+        p = (scratch.data_ptr() + 7) & ~7
+        p_info = p + 8 * (2 * n + 1)
+        p_linf = p_info + 8 * (n + 1)
+        wp = p_linf + 4 * n
+        p_rows = wp + 4 * (2 * n + 1)
+        p_keep = p_rows + 4 * n
+        off = p - scratch.data_ptr()
+        buf = scratch[off:off + 8 * (2 * n + 1)].view(torch.float64)
+        info = scratch[off + 8 * (2 * n + 1):off + 8 * (3 * n + 2)].view(torch.float64)
+        linf = scratch[off + 8 * (3 * n + 2):off + 8 * (3 * n + 2) + 4 * n].view(torch.float32)
+        check(L.flagg_row_reduce(u.view(), g_ptr, 0, p, (p + 8 * n) if g_ptr else None, p_linf,
                                  (p + 16 * n) if g_ptr else None, st), "flagg_row_reduce")
         if group is not None:
             all_reduce(buf, group, "sum")
             if use_linf:
                 all_reduce(linf, group, "max")
-        ne = None
-        if num_examples is not None:
-            ne = torch.tensor([float(int(x)) for x in num_examples], dtype=torch.float64).to(u.device, non_blocking=True)
-        rows = torch.empty(n, dtype=torch.int32, device=u.device)
-        w = torch.empty(2 * n + 1, dtype=torch.float32, device=u.device)          # w1, w2, divisor
-        info = torch.empty(n + 1, dtype=torch.float64, device=u.device)           # per-client value; the last slot holds the two counts
-        keep = torch.empty(n, dtype=torch.uint8, device=u.device)
-        wp = w.data_ptr()
+        ne = _examples_on_device(num_examples, u.device) if num_examples is not None else None
         check(L.flagg_round_weights(int(rule), n, None if use_linf else p, (p + 8 * n) if has_g0 else None,
-                                    (p + 16 * n) if has_g0 else None, linf.data_ptr() if use_linf else None,
-                                    ne.data_ptr() if ne is not None else None, float(p0), float(p1), rows.data_ptr(), wp, wp + 4 * n,
-                                    wp + 8 * n, info.data_ptr(), info.data_ptr() + 8 * n, keep.data_ptr(), st), "flagg_round_weights")
+                                    (p + 16 * n) if has_g0 else None, p_linf if use_linf else None,
+                                    ne.data_ptr() if ne is not None else None, float(p0), float(p1), p_rows, wp, wp + 4 * n,
+                                    wp + 8 * n, p_info, p_info + 8 * n, p_keep, st), "flagg_round_weights")
         out = torch.empty(u.d, dtype=torch.float32, device=u.device) if outs is None else None
         if outs is not None:
             u._bind(outs)
         try:
-            check(L.flagg_row_combine_dev(u.view(), n, rows.data_ptr(), wp, wp + 4 * n, wp + 8 * n,
+            check(L.flagg_row_combine_dev(u.view(), n, p_rows, wp, wp + 4 * n, wp + 8 * n,
                                           out.data_ptr() if out is not None else None, None, None, st), "flagg_row_combine_dev")
         finally:
             if outs is not None:
@@ -452,6 +459,19 @@ def weighted_round(u: Updates, rule: int, num_examples=None, g0_flat: Optional[t
         h = info.cpu()                                                            # the round's one synchronisation
         counts = h[n:].view(torch.int32)
         return out, h[:n].numpy().copy(), int(counts[0]), int(counts[1])
+
+
+_EXAMPLES = [None, None, None]     # (tuple(num_examples), device, FP64 device tensor) of the latest round
+
+
+def _examples_on_device(num_examples, device) -> torch.Tensor:
+    """The clients' example counts as FP64 on the device.  Rounds of one experiment repeat the same counts
+    (the clients' dataset sizes): the upload, a pageable copy, is made when they change."""
+    key = tuple(int(x) for x in num_examples)
+    if _EXAMPLES[0] != key or _EXAMPLES[1] != device:
+        t = torch.tensor([float(x) for x in key], dtype=torch.float64).to(device)
+        _EXAMPLES[0], _EXAMPLES[1], _EXAMPLES[2] = key, device, t
+    return _EXAMPLES[2]
 
 
 CENTER_ROWS = 31   # rows whose coordinate-wise median centres the Gram matrix

@@ -100,6 +100,47 @@ def test_c2_median_multimodal_cnn_bit_exact():
     assert np.array_equal(bits(flat(res).cpu().numpy()), bits(ref))
 
 
+@pytest.mark.parametrize("layout", ["separate", "dense"])
+@pytest.mark.parametrize("shape", ["multimodal_cnn_P22", "resnet18_sized"])
+def test_c2_krum_and_multikrum(shape, layout):
+    """C2's cohort (20 clients, f = 4) through KrumDefense / MultiKrumDefense: the small-cohort distance kernel
+    (pair groups: tile::gather4 feed on separately allocated tensors, 2-D box feed on rows of one matrix, 22 ragged
+    tensors or one of 11.69 M columns) against FP64 distances, the ranking against FP64 scores, the Multi-Krum
+    mean bit for bit on sampled columns."""
+    from src.defenses import KrumDefense, MultiKrumDefense
+    n, f = 20, 4
+    seg = MULTIMODAL_CNN if shape == "multimodal_cnn_P22" else [11_689_512]
+    d = sum(seg)
+    X = device_rows(n, d, f, 29)
+    if layout == "separate":
+        ups = separate(X, seg)
+    else:
+        offs = np.concatenate([[0], np.cumsum(seg)]).astype(int)
+        mats = [torch.zeros((n, (s + 3) & ~3), device="cuda") for s in seg]          # one matrix per tensor, 16-byte row pitch
+        for p, s in enumerate(seg):
+            mats[p][:, :s] = X[:, offs[p]:offs[p + 1]]
+        ups = [[mats[p][i, :seg[p]] for p in range(len(seg))] for i in range(n)]
+    D64 = fp64_distances(X)
+    s64 = oracle64.krum_scores64(D64, f)
+    off = ~np.eye(n, dtype=bool)
+    for cls, m in ((KrumDefense, 1), (MultiKrumDefense, 10)):
+        defense = cls({"num_malicious": f, "multi_k": m})
+        res = defense.aggregate(ups, [100] * n)
+        D = defense._compute_distances(ups)
+        err = np.abs(D[off] - D64[off]) / D64[off]
+        report(f"c2_krum_{shape}_{layout}_m{m}", max_rel_err=float(err.max()))
+        assert err.max() <= 1e-5 and err.max() <= 2e-6                         # direct differences: no cancellation
+        np.testing.assert_allclose(np.array(defense.client_scores), s64, rtol=1e-5)
+        check_ranking(defense.selected_clients, defense.rejected_clients, s64, m, f"c2_krum_{shape}_{layout}_m{m}")
+        assert set(defense.rejected_clients[-f:]) == set(range(f))             # the Byzantine rows rank last
+        if m == 1:
+            assert res is ups[defense.selected_clients[0]]                     # krum.py:180-181 returns the client's own list
+        else:
+            cols = torch.from_numpy(np.random.RandomState(1).randint(0, d, 2048)).cuda()
+            ref = oracle64.combine_seq32(X[:, cols].cpu().numpy(), None, None, np.float32(m), rows=defense.selected_clients)
+            assert np.array_equal(bits(flat(res)[cols].cpu().numpy()), bits(ref))
+
+
 # ---------------------------------------------------------------------------------------
 # C4 shard: Multi-Krum
 # ---------------------------------------------------------------------------------------

@@ -29,7 +29,8 @@ def timed(fn, steps=20, warm=5):
 
 for n in ns:
     X = torch.randn((n, d), device="cuda") * 1e-3 + 0.05
-    ups = [[torch.empty(d, device="cuda").copy_(X[i])] for i in range(n)]
+    # LAYOUT=dense: rows of one matrix (2-D box feed); default: separately allocated rows (the reference's layout: gather4 feed)
+    ups = [[X[i]] for i in range(n)] if os.environ.get("LAYOUT") == "dense" else [[torch.empty(d, device="cuda").copy_(X[i])] for i in range(n)]
     u = engine.Updates(ups)
     t_impl = {}
     for impl in ("jobs", "pairs"):
