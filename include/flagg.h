@@ -191,7 +191,7 @@ int flagg_gram(const flagg_view* v, const float* center, int accumulate, double*
 /* Small cohorts (n <= 32: the reference's default 10-20 clients): D2 (device, FP64, n*n row-major,
  * symmetric, zero diagonal) = squared pairwise distances ||x_i - x_j||^2 by DIRECT differences, as
  * krum.py:95 forms them (torch.norm(f_i - f_j)): one pass over X, no centre vector and therefore no
- * centre pass, no cancellation; packed fp32x2 subtract + fma per pair and column, fp32 partial sums
+ * centre pass, no cancellation; one fp32 subtract + fma per pair and column, fp32 partial sums
  * of at most 1024 columns folded into FP64.  Non-finite rows give NaN / inf entries by IEEE
  * arithmetic, exactly where the reference's distances are NaN / inf.  With the parameter dimension
  * sharded, partial D2's add: all-reduce them before flagg_krum_scores_from_sqdist.
