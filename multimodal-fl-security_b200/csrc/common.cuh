@@ -77,6 +77,7 @@ struct flagg_view {
     std::vector<int64_t> seg_numel, seg_start;              // host copies
     std::vector<int64_t> unit_start[flagg::NUM_GRAN];
     std::vector<const void*> seg_ptrs;                      // host copy [n*P]
+    std::vector<char> upload;                               // host image of d_tables (one H2D copy at creation)
     void* d_tables = nullptr;      // one allocation holding all device tables
     void* d_out_ptrs = nullptr;    // [P] slot inside d_tables for flagg_view_set_outputs
     std::vector<void*> out_ptrs;   // host copy of the output table (empty = flat output)

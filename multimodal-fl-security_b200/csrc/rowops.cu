@@ -128,27 +128,41 @@ row_reduce_kernel(ViewDev v, const float* __restrict__ g0, double* __restrict__ 
     }
 }
 
-__global__ void row_reduce_finalize(const double* __restrict__ part_ss, const double* __restrict__ part_dot,
-                                    const float* __restrict__ part_linf, const double* __restrict__ part_g0,
-                                    int nblocks, int n, double* sumsq, double* dot, float* linf, double* g0_sumsq) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) {
-        double ss = 0.0, dt = 0.0;
-        float mx = 0.f;
-        for (int b = 0; b < nblocks; ++b) {
-            ss += part_ss[size_t(b) * n + i];
-            dt += part_dot[size_t(b) * n + i];
-            mx = fmaxf(mx, part_linf[size_t(b) * n + i]);
-        }
+// One warp per client (plus one for ||g0||^2): lanes stride over the per-CTA partials, then a fixed-shape shuffle tree
+// -- the same order every run.  (One THREAD per client walked up to 592 dependent L2 round trips: 50-100 us, a
+// quarter of a whole clipping round at the small BASELINE shapes.)
+constexpr int RRF_THREADS = 128;
+__global__ void __launch_bounds__(RRF_THREADS)
+row_reduce_finalize(const double* __restrict__ part_ss, const double* __restrict__ part_dot,
+                    const float* __restrict__ part_linf, const double* __restrict__ part_g0,
+                    int nblocks, int n, double* sumsq, double* dot, float* linf, double* g0_sumsq) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (RRF_THREADS / 32) + (threadIdx.x >> 5);      // warp-uniform
+    if (i > n) return;
+    if (i == n) {
+        if (!g0_sumsq) return;
+        double t = 0.0;
+        for (int b = lane; b < nblocks; b += 32) t += part_g0[b];
+        t = warp_sum(t);
+        if (lane == 0) *g0_sumsq = t;
+        return;
+    }
+    double ss = 0.0, dt = 0.0;
+    float mx = 0.f;
+#pragma unroll 4
+    for (int b = lane; b < nblocks; b += 32) {
+        ss += part_ss[size_t(b) * n + i];
+        dt += part_dot[size_t(b) * n + i];
+        mx = fmaxf(mx, part_linf[size_t(b) * n + i]);
+    }
+    ss = warp_sum(ss);
+    dt = warp_sum(dt);
+    mx = warp_max(mx);
+    if (lane == 0) {
         if (sumsq) sumsq[i] = ss;
         if (dot) dot[i] = dt;
         // torch.max(torch.abs(x)) propagates NaN (differential_privacy.py:230); fmaxf does not.
         if (linf) linf[i] = (ss != ss) ? __int_as_float(0x7fc00000) : mx;
-    }
-    if (i == 0 && g0_sumsq) {
-        double t = 0.0;
-        for (int b = 0; b < nblocks; ++b) t += part_g0[b];
-        *g0_sumsq = t;
     }
 }
 
@@ -434,7 +448,7 @@ int flagg_row_reduce(const flagg_view* cv, const float* g0, int centered, double
     else if (g0) rc = launch(row_reduce_kernel<false, true, false>);
     else rc = launch(row_reduce_kernel<false, false, false>);
     if (rc != FLAGG_OK) return rc;
-    row_reduce_finalize<<<(n + 127) / 128, 128, 0, st>>>(part_ss, part_dot, part_linf, part_g0, nblocks, n,
+    row_reduce_finalize<<<(n + 1 + RRF_THREADS / 32 - 1) / (RRF_THREADS / 32), RRF_THREADS, 0, st>>>(part_ss, part_dot, part_linf, part_g0, nblocks, n,
                                                          sumsq, dot, linf, g0_sumsq);
     FLAGG_CUDA(cudaGetLastError());
     return FLAGG_OK;
@@ -617,7 +631,7 @@ extern "C" int flagg_row_reduce_static(const flagg_view* cv, const float* g0, in
     else if (g0) rc = launch(row_reduce_kernel<false, true, false>);
     else rc = launch(row_reduce_kernel<false, false, false>);
     if (rc != FLAGG_OK) return rc;
-    row_reduce_finalize<<<(n + 127) / 128, 128, 0, st>>>(part_ss, part_dot, part_linf, part_g0, nblocks, n,
+    row_reduce_finalize<<<(n + 1 + RRF_THREADS / 32 - 1) / (RRF_THREADS / 32), RRF_THREADS, 0, st>>>(part_ss, part_dot, part_linf, part_g0, nblocks, n,
                                                          sumsq, dot, linf, g0_sumsq);
     FLAGG_CUDA(cudaGetLastError());
     return FLAGG_OK;
