@@ -492,8 +492,9 @@ int flagg_row_combine(const flagg_view* cv, int m, const int32_t* rows, const fl
     const int n = v->dev.n;
     FLAGG_REQUIRE(m >= 1, "flagg_row_combine: m must be >= 1 (got %d)", m);
     FLAGG_REQUIRE(rows || m == n, "flagg_row_combine: rows == NULL requires m == n");
-    std::vector<int32_t> hr(m);
-    std::vector<float> hw(2 * size_t(m));
+    // one host block, one upload: w1 [m] | w2 [m] | rows [m]
+    std::vector<float> hw(3 * size_t(m));
+    int32_t* hr = reinterpret_cast<int32_t*>(hw.data() + 2 * size_t(m));
     for (int j = 0; j < m; ++j) {
         hr[j] = rows ? rows[j] : j;
         FLAGG_REQUIRE(hr[j] >= 0 && hr[j] < n, "flagg_row_combine: rows[%d]=%d out of range", j, hr[j]);
@@ -505,8 +506,7 @@ int flagg_row_combine(const flagg_view* cv, int m, const int32_t* rows, const fl
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     float* d_w = static_cast<float*>(v->d_scratch);
     int* d_rows = reinterpret_cast<int*>(d_w + 2 * size_t(m));
-    FLAGG_CUDA(cudaMemcpyAsync(d_w, hw.data(), sizeof(float) * 2 * size_t(m), cudaMemcpyHostToDevice, st));
-    FLAGG_CUDA(cudaMemcpyAsync(d_rows, hr.data(), sizeof(int32_t) * size_t(m), cudaMemcpyHostToDevice, st));
+    FLAGG_CUDA(cudaMemcpyAsync(d_w, hw.data(), sizeof(float) * 3 * size_t(m), cudaMemcpyHostToDevice, st));
     return row_combine_launch(v, m, d_rows, d_w, d_w + m, divisor, nullptr, out, nullptr, nullptr, 0, st);
 }
 
