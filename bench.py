@@ -483,7 +483,7 @@ def c2_defenses(dist_on, with_cpu):
     t = time_steps(lambda: kd.aggregate(ups, [1] * n), 10, 3, dist_on) / 10
     out["krum_C2_20x11.69M_f4"] = {"n": n, "d": d, "ms": t * 1e3, "GBps": 4.0 * n * d / t / 1e9, "steps": 10,
                                    "roofline_frac_hbm": 4.0 * n * d / t / 1e9 / hbm,
-                                   "api": "KrumDefense.aggregate(separately allocated device rows): centre + Gram + scores + argsort"}
+                                   "api": "KrumDefense.aggregate(separately allocated device rows): squared distances by direct differences (flagg_sqdist) + scores + argsort"}
     del ups
     if with_cpu:
         out["trimmed_mean_C2_20x11.69M_k2"]["cpu_baseline"] = cpu_trimmed_mean_c2()
