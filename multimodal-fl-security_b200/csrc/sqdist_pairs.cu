@@ -4,7 +4,7 @@
 // sqdist_small.cu cuts the rows into blocks of 8 and gives every warp a job of at most 64 pairs; from n = 17 the jobs
 // are uneven (32 / 28 / 6 pairs at n = 20), every stage ends in a CTA barrier that waits for the heaviest job, and the
 // kernel ran at 2.3 TB/s with the FP32 pipe a third busy (profiles/r02_ncu_sqdist_n20_summary.txt).  Here the
-// n (n - 1) / 2 pairs, enumerated row-major, are cut into H equal groups; a warp owns ONE group (at most ~100 fp32
+// n (n - 1) / 2 pairs, enumerated row-major, are cut into H equal groups; a warp owns ONE group (at most 124 fp32
 // accumulators in registers, lane = column) and computes it for a whole 32-column quarter at a time from N
 // shared-memory loads.  Every warp of the kernel executes the same instruction count per quarter, so the barrier that
 // closes a stage finds the warps together, and there are N loads per 2 G arithmetic instructions instead of 12 per 64.
@@ -31,12 +31,13 @@ constexpr int SP_MAX_STAGES = 8;
 constexpr int SP_MAX_GROUPS = 4;
 
 __host__ __device__ constexpr int sp_pairs(int n) { return n * (n - 1) / 2; }
-// Groups: the accumulators of a group, the N row values and ~36 registers of addressing fit the register cap; 1, 2 or 4
-// groups, so that the warps a scheduler holds (warp id mod 4) all run the code of ONE group -- with 3, 5 or 6 groups
-// the schedulers interleave different instruction streams and the kernel starves on instruction fetch (n = 32 with
-// five groups: 0.93 ms against 0.66 for the row-block kernel).  More than 4 groups: not served (sp_serves).
-// registers per thread the kernel is built for: 168 (12 warps per SM) up to 29 clients; 30-32 clients would need 8 groups
-// there, so they get 4 groups of up to 124 accumulators in ~200 registers (8 warps per SM)
+// Groups: the accumulators of a group, the N row values and ~36 registers of addressing fit the register cap.  1, 2 or 4
+// groups only: a CTA of 2 or 4 warps puts the same number of warps on each of the SM's four schedulers (warp id mod 4;
+// five warps per CTA leave them 3 / 3 / 2 / 2) and the warps a scheduler holds all run the code of ONE group.  Builds
+// with 3, 5 and 6 groups measured 0.9-2.3 ms at n = 32 against 0.66 for the row-block kernel -- measured with the old
+// 2400-instruction epilogue per group (see the end of sp_run), so part of that was code size, not the group count.
+// Registers per thread the kernel is built for: 168 (12 warps per SM) up to 29 clients; 30-32 clients would need 8 groups
+// there, so they get 4 groups of up to 124 accumulators in ~190 registers (8 warps per SM).
 __host__ __device__ constexpr int sp_reg_cap(int n) { return n >= 30 ? 200 : SP_REG_CAP; }
 __host__ __device__ constexpr int sp_groups(int n) {
     const int gmax = sp_reg_cap(n) - n - 36;
@@ -123,6 +124,7 @@ __device__ __forceinline__ void sp_run(const ViewDev& v, int total_units, double
     constexpr int QU = QW <= 2 ? QW : 1;                           // four quarters: a loop, not four copies (instruction cache)
     constexpr int NPAD = sp_npad(N), UNIT = NPAD * 128;            // floats per stage: one 128-column unit of every row
     constexpr int ROWS = (N + WP - 1) / WP;                        // rows a warp copies
+    static_assert(STAGES * UNIT >= WP * 32 * 33, "the ring must hold the epilogue's [32][33] tile of every warp");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, cs = warp / H;
     // stage k of CTA b is unit k * grid + b
     const int u0 = blockIdx.x, ustep = gridDim.x;
