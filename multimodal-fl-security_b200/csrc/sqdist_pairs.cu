@@ -36,9 +36,14 @@ __host__ __device__ constexpr int sp_pairs(int n) { return n * (n - 1) / 2; }
 // five warps per CTA leave them 3 / 3 / 2 / 2) and the warps a scheduler holds all run the code of ONE group.  Builds
 // with 3, 5 and 6 groups measured 0.9-2.3 ms at n = 32 against 0.66 for the row-block kernel -- measured with the old
 // 2400-instruction epilogue per group (see the end of sp_run), so part of that was code size, not the group count.
-// Registers per thread the kernel is built for: 168 (12 warps per SM) up to 29 clients; 30-32 clients would need 8 groups
-// there, so they get 4 groups of up to 124 accumulators in ~190 registers (8 warps per SM).
-__host__ __device__ constexpr int sp_reg_cap(int n) { return n >= 30 ? 200 : SP_REG_CAP; }
+// Registers per thread the kernel is built for: 168 (12 warps per SM) by default.  Fewer, larger groups won wherever
+// they fit the register file -- 22-25 clients: 2 groups of up to 150 accumulators in 224 registers (8 warps per SM;
+// n = 22: 0.267 -> 0.240 ms, n = 24: 0.320 -> 0.299 against 4 groups), 26-27: 2 groups of up to 176 in 255 (n = 26:
+// 0.356 -> 0.336); 30-32 clients would need 8 groups at 168, so they get 4 groups of up to 124 accumulators in ~190
+// registers.  One group of up to 190 for 17-20 clients was measured too: better at n = 17, worse at 18 and 20 -- left.
+__host__ __device__ constexpr int sp_reg_cap(int n) {
+    return n >= 30 ? 200 : (n >= 26 && n <= 27 ? 255 : (n >= 22 && n <= 25 ? 224 : SP_REG_CAP));
+}
 __host__ __device__ constexpr int sp_groups(int n) {
     const int gmax = sp_reg_cap(n) - n - 36;
     const int h = sp_pairs(n) <= gmax ? 1 : (sp_pairs(n) + gmax - 1) / gmax;
